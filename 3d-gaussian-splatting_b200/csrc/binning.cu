@@ -1,0 +1,163 @@
+// binning.cu — stage 2a/2b/2d: scan of per-block tile counts, load-balanced key emission, per-tile
+// ranges.  Integer work, bit-exact against oracle.bin_tiles / sort_and_ranges, which
+// restate gsplat isect_tiles / isect_offset_encode as called through gsplat_backend.py:168-182.
+#include "common.cuh"
+
+#define EMIT_THREADS 256  // must equal PROJ_THREADS: block b owns Gaussians [256 b, 256 b + 256)
+
+namespace {
+
+__global__ void __launch_bounds__(1024)
+bin_scan_kernel(const int64_t* __restrict__ block_sums, int64_t nblocks, int64_t* __restrict__ block_offsets,
+                int64_t* __restrict__ total) {
+    __shared__ int64_t warp_tot[32];
+    __shared__ int64_t carry_s;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    for (int64_t base = 0; base < nblocks; base += 1024) {
+        int64_t i = base + threadIdx.x;
+        int64_t v = i < nblocks ? block_sums[i] : 0;
+        int64_t inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int64_t n = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += n;
+        }
+        if (lane == 31) warp_tot[wid] = inc;
+        __syncthreads();
+        if (wid == 0) {
+            int64_t w = warp_tot[lane];
+            int64_t winc = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int64_t n = __shfl_up_sync(0xffffffffu, winc, o);
+                if (lane >= o) winc += n;
+            }
+            warp_tot[lane] = winc - w;  // exclusive
+        }
+        __syncthreads();
+        int64_t carry = carry_s;
+        int64_t excl = carry + warp_tot[wid] + inc - v;
+        if (i < nblocks) block_offsets[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) total[0] = carry_s;
+}
+
+__global__ void __launch_bounds__(EMIT_THREADS)
+bin_emit_kernel(const float* __restrict__ splats, const int32_t* __restrict__ radii,
+                const int32_t* __restrict__ tiles_per_gauss, const int64_t* __restrict__ block_offsets,
+                int64_t N, int tile_w, int tile_h, int64_t M, int64_t* __restrict__ isect_ids,
+                int32_t* __restrict__ flatten_ids, int64_t* __restrict__ cum_tiles) {
+    __shared__ int s_excl[EMIT_THREADS + 1];
+    __shared__ int s_minx[EMIT_THREADS], s_miny[EMIT_THREADS], s_bw[EMIT_THREADS];
+    __shared__ uint32_t s_depth[EMIT_THREADS];
+    __shared__ int s_warp[EMIT_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int64_t g = (int64_t)blockIdx.x * EMIT_THREADS + tid;
+    int cnt = 0;
+    if (g < N) {
+        cnt = tiles_per_gauss[g];
+        if (cnt > 0) {
+            const float4 r0 = __ldg(reinterpret_cast<const float4*>(splats) + 3 * g);
+            const float depth = __ldg(splats + SPLAT_F * g + 9);
+            const int2 rad = __ldg(reinterpret_cast<const int2*>(radii) + g);
+            float tile_x = r0.x / (float)TILE, tile_y = r0.y / (float)TILE;
+            float trx = (float)rad.x / (float)TILE, try_ = (float)rad.y / (float)TILE;
+            float fw = (float)tile_w, fh = (float)tile_h;
+            int minx = (int)fminf(fmaxf(floorf(tile_x - trx), 0.f), fw);
+            int maxx = (int)fminf(fmaxf(ceilf(tile_x + trx), 0.f), fw);
+            int miny = (int)fminf(fmaxf(floorf(tile_y - try_), 0.f), fh);
+            s_minx[tid] = minx; s_miny[tid] = miny; s_bw[tid] = maxx - minx;
+            s_depth[tid] = __float_as_uint(depth);
+        }
+    }
+    // block exclusive scan of cnt
+    int inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    if (lane == 31) s_warp[wid] = inc;
+    __syncthreads();
+    int woff = 0;
+#pragma unroll
+    for (int w = 0; w < EMIT_THREADS / 32; ++w) woff += (w < wid) ? s_warp[w] : 0;
+    const int excl = woff + inc - cnt;
+    s_excl[tid] = excl;
+    if (tid == EMIT_THREADS - 1) s_excl[EMIT_THREADS] = excl + cnt;
+    const int64_t boff = block_offsets[blockIdx.x];
+    if (cum_tiles != nullptr && g < N) cum_tiles[g] = boff + excl + cnt;
+    __syncthreads();
+    const int total = s_excl[EMIT_THREADS];
+    for (int k = tid; k < total; k += EMIT_THREADS) {
+        // largest i with s_excl[i] <= k  (upper_bound - 1)
+        int lo = 0, hi = EMIT_THREADS;  // invariant: s_excl[lo] <= k < s_excl[hi]
+        while (hi - lo > 1) {
+            int mid = (lo + hi) >> 1;
+            if (s_excl[mid] <= k) lo = mid; else hi = mid;
+        }
+        const int kk = k - s_excl[lo];
+        const int bw = s_bw[lo];
+        const int ty = s_miny[lo] + kk / bw, tx = s_minx[lo] + kk % bw;
+        const int64_t tile_id = (int64_t)ty * tile_w + tx;
+        const int64_t out = boff + k;
+        if (out < M) {
+            isect_ids[out] = (tile_id << 32) | (int64_t)s_depth[lo];
+            flatten_ids[out] = (int32_t)((int64_t)blockIdx.x * EMIT_THREADS + lo);
+        }
+    }
+}
+
+__global__ void tile_ranges_kernel(const int64_t* __restrict__ ids, int64_t M, int n_tiles, int32_t* __restrict__ offsets) {
+    int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= M) return;
+    int cur = (int)(ids[idx] >> 32);
+    if (idx == 0) {
+        for (int t = 0; t <= cur; ++t) offsets[t] = 0;
+    } else {
+        int prev = (int)(ids[idx - 1] >> 32);
+        for (int t = prev + 1; t <= cur; ++t) offsets[t] = (int32_t)idx;
+    }
+    if (idx == M - 1)
+        for (int t = cur + 1; t < n_tiles; ++t) offsets[t] = (int32_t)M;
+}
+
+}  // namespace
+
+extern "C" int b200_bin_scan(const int64_t* block_sums, int64_t nblocks, int64_t* block_offsets, int64_t* total, void* stream) {
+    B200_REQUIRE(nblocks >= 0 && total, "bad args");
+    B200_REQUIRE(nblocks == 0 || (block_sums && block_offsets), "null pointer");
+    bin_scan_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(block_sums, nblocks, block_offsets, total);
+    return b200_check_launch("bin_scan");
+}
+
+extern "C" int b200_bin_emit(const float* splats, const int32_t* radii, const int32_t* tiles_per_gauss,
+                             const int64_t* block_offsets, int64_t N, int width, int height, int64_t M,
+                             int64_t* isect_ids, int32_t* flatten_ids, int64_t* cum_tiles, void* stream) {
+    B200_REQUIRE(N >= 0 && M >= 0 && width > 0 && height > 0, "bad sizes");
+    B200_REQUIRE(M < ((int64_t)1 << 30), "too many intersections (M >= 2^30)");
+    if (N == 0) return B200_OK;
+    B200_REQUIRE(splats && radii && tiles_per_gauss && block_offsets, "null pointer");
+    B200_REQUIRE(M == 0 || (isect_ids && flatten_ids), "null output");
+    int tile_w = (width + TILE - 1) / TILE, tile_h = (height + TILE - 1) / TILE;
+    bin_emit_kernel<<<(unsigned)b200_project_blocks(N), EMIT_THREADS, 0, (cudaStream_t)stream>>>(
+        splats, radii, tiles_per_gauss, block_offsets, N, tile_w, tile_h, M, isect_ids, flatten_ids, cum_tiles);
+    return b200_check_launch("bin_emit");
+}
+
+extern "C" int b200_tile_ranges(const int64_t* sorted_isect_ids, int64_t M, int n_tiles, int32_t* offsets, void* stream) {
+    B200_REQUIRE(M >= 0 && n_tiles > 0 && offsets, "bad args");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (M == 0) {
+        cudaMemsetAsync(offsets, 0, sizeof(int32_t) * (size_t)n_tiles, st);
+        return b200_check_launch("tile_ranges(memset)");
+    }
+    B200_REQUIRE(sorted_isect_ids, "null pointer");
+    tile_ranges_kernel<<<(unsigned)((M + 255) / 256), 256, 0, st>>>(sorted_isect_ids, M, n_tiles, offsets);
+    return b200_check_launch("tile_ranges");
+}

@@ -1,0 +1,471 @@
+// project_sh.cu — stage 1 (EWA projection + SH colour + tile count, fused) and stage 4b (its VJP).
+//
+// Semantics follow gsplat 1.5.x as the reference calls it (src/backends/gsplat_backend.py:168-182;
+// SURVEY.md Appendix A.1, A.2, A.6).  One thread per Gaussian; the 48-B splat record is the only
+// per-Gaussian float output so the blend stages gather three 16-B vectors per Gaussian.
+#include "common.cuh"
+
+#define PROJ_THREADS 256
+
+namespace {
+
+constexpr float SH_C0 = 0.2820947917738781f;
+constexpr float SH_C1 = 0.48860251190292f;
+constexpr float SH_C2A = 0.5462742152960395f;
+constexpr float SH_C2B = 1.092548430592079f;
+constexpr float SH_C2C = 0.9461746957575601f;
+constexpr float SH_C2D = 0.3153915652525201f;
+constexpr float SH_C3A = 0.5900435899266435f;
+constexpr float SH_C3B = 1.445305721320277f;
+constexpr float SH_C3C = 2.285228997322329f;
+constexpr float SH_C3D = 0.4570457994644658f;
+constexpr float SH_C3E = 1.865881662950577f;
+constexpr float SH_C3F = 1.119528997770346f;
+
+struct Proj {
+    float pcx, pcy, pcz;   // camera-space mean
+    float Rq[9];           // rotation from the normalised quaternion
+    float qn[4];           // normalised quaternion
+    float inv_norm;        // 1/|q|
+    float Wm[9];           // R * Rq * diag(s)
+    float J00, J02, J11, J12;
+    float T[6];            // J * Wm (2x3)
+    float tx, ty, rz;
+    bool clamp_x, clamp_y;
+    float a, b, c, det;    // blurred 2-D covariance and determinant
+    float mx, my;
+};
+
+// Forward projection up to the conic; returns false if culled by depth or determinant.
+__device__ __forceinline__ bool project_core(const Cam& cam, float px, float py, float pz, float4 q,
+                                             float sx, float sy, float sz, Proj& P) {
+    const float* R = cam.R;
+    P.pcx = R[0] * px + R[1] * py + R[2] * pz + cam.t[0];
+    P.pcy = R[3] * px + R[4] * py + R[5] * pz + cam.t[1];
+    P.pcz = R[6] * px + R[7] * py + R[8] * pz + cam.t[2];
+    if (!(P.pcz >= cam.near_plane) || !(P.pcz <= cam.far_plane)) return false;
+
+    float n2 = q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w;
+    P.inv_norm = rsqrtf(n2);
+    // quaternion stored (w,x,y,z) == (q.x,q.y,q.z,q.w)
+    float w = q.x * P.inv_norm, x = q.y * P.inv_norm, y = q.z * P.inv_norm, z = q.w * P.inv_norm;
+    P.qn[0] = w; P.qn[1] = x; P.qn[2] = y; P.qn[3] = z;
+    float* Rq = P.Rq;
+    Rq[0] = 1.f - 2.f * (y * y + z * z); Rq[1] = 2.f * (x * y - w * z); Rq[2] = 2.f * (x * z + w * y);
+    Rq[3] = 2.f * (x * y + w * z); Rq[4] = 1.f - 2.f * (x * x + z * z); Rq[5] = 2.f * (y * z - w * x);
+    Rq[6] = 2.f * (x * z - w * y); Rq[7] = 2.f * (y * z + w * x); Rq[8] = 1.f - 2.f * (x * x + y * y);
+    const float s[3] = {sx, sy, sz};
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            P.Wm[i * 3 + j] = (R[i * 3 + 0] * Rq[0 * 3 + j] + R[i * 3 + 1] * Rq[1 * 3 + j] +
+                               R[i * 3 + 2] * Rq[2 * 3 + j]) * s[j];
+
+    float tanx = 0.5f * cam.W / cam.fx, tany = 0.5f * cam.H / cam.fy;
+    float lim_xp = (cam.W - cam.cx) / cam.fx + 0.3f * tanx;
+    float lim_xn = cam.cx / cam.fx + 0.3f * tanx;
+    float lim_yp = (cam.H - cam.cy) / cam.fy + 0.3f * tany;
+    float lim_yn = cam.cy / cam.fy + 0.3f * tany;
+    float rz = 1.f / P.pcz;
+    float rz2 = rz * rz;
+    float xr = P.pcx * rz, yr = P.pcy * rz;
+    P.clamp_x = !(xr <= lim_xp && xr >= -lim_xn);
+    P.clamp_y = !(yr <= lim_yp && yr >= -lim_yn);
+    P.tx = P.pcz * fminf(lim_xp, fmaxf(-lim_xn, xr));
+    P.ty = P.pcz * fminf(lim_yp, fmaxf(-lim_yn, yr));
+    P.rz = rz;
+    P.J00 = cam.fx * rz;
+    P.J02 = -cam.fx * P.tx * rz2;
+    P.J11 = cam.fy * rz;
+    P.J12 = -cam.fy * P.ty * rz2;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        P.T[j] = P.J00 * P.Wm[j] + P.J02 * P.Wm[6 + j];
+        P.T[3 + j] = P.J11 * P.Wm[3 + j] + P.J12 * P.Wm[6 + j];
+    }
+    float s00 = P.T[0] * P.T[0] + P.T[1] * P.T[1] + P.T[2] * P.T[2];
+    float s01 = P.T[0] * P.T[3] + P.T[1] * P.T[4] + P.T[2] * P.T[5];
+    float s11 = P.T[3] * P.T[3] + P.T[4] * P.T[4] + P.T[5] * P.T[5];
+    P.a = s00 + cam.eps2d;
+    P.b = s01;
+    P.c = s11 + cam.eps2d;
+    P.det = P.a * P.c - P.b * P.b;
+    P.mx = cam.fx * P.pcx * rz + cam.cx;
+    P.my = cam.fy * P.pcy * rz + cam.cy;
+    return P.det > 0.f;
+}
+
+// Opacity-aware rectangular extent and screen cull.
+__device__ __forceinline__ bool radius_and_cull(const Cam& cam, const Proj& P, float opac, int& rx, int& ry) {
+    if (!(opac >= ALPHA_THRESHOLD)) return false;
+    float extend = fminf(3.33f, sqrtf(2.0f * logf(opac / ALPHA_THRESHOLD)));
+    float frx = ceilf(extend * sqrtf(P.a));
+    float fry = ceilf(extend * sqrtf(P.c));
+    if (frx <= cam.radius_clip && fry <= cam.radius_clip) return false;
+    if (P.mx + frx <= 0.f || P.mx - frx >= (float)cam.W || P.my + fry <= 0.f || P.my - fry >= (float)cam.H)
+        return false;
+    rx = (int)frx;
+    ry = (int)fry;
+    return rx > 0 && ry > 0;
+}
+
+// Real SH basis up to `DEG` for unit direction (x,y,z): B[(DEG+1)^2].
+template <int DEG>
+__device__ __forceinline__ void sh_basis(float x, float y, float z, float* B) {
+    B[0] = SH_C0;
+    if (DEG >= 1) {
+        B[1] = -SH_C1 * y; B[2] = SH_C1 * z; B[3] = -SH_C1 * x;
+    }
+    if (DEG >= 2) {
+        float z2 = z * z, fT0B = -SH_C2B * z, fC1 = x * x - y * y, fS1 = 2.f * x * y;
+        B[4] = SH_C2A * fS1; B[5] = fT0B * y; B[6] = SH_C2C * z2 - SH_C2D; B[7] = fT0B * x; B[8] = SH_C2A * fC1;
+        if (DEG >= 3) {
+            float fT0C = -SH_C3C * z2 + SH_C3D, fT1B = SH_C3B * z;
+            float fC2 = x * fC1 - y * fS1, fS2 = x * fS1 + y * fC1;
+            B[9] = -SH_C3A * fS2; B[10] = fT1B * fS1; B[11] = fT0C * y;
+            B[12] = z * (SH_C3E * z2 - SH_C3F); B[13] = fT0C * x; B[14] = fT1B * fC1; B[15] = -SH_C3A * fC2;
+        }
+    }
+}
+
+// Coefficient fetch: NV = number of 16-B vectors holding the first 3*(DEG+1)^2 floats.
+template <int DEG>
+struct ShCount {
+    static constexpr int NB = (DEG + 1) * (DEG + 1);
+    static constexpr int NF = 3 * NB;
+    static constexpr int NV = (NF + 3) / 4;
+};
+
+template <int DEG>
+__device__ __forceinline__ void load_sh(const float* __restrict__ shs, int64_t g, int sh_coeffs, bool vec_ok,
+                                        float* c /* NV*4 */) {
+    constexpr int NV = ShCount<DEG>::NV;
+    constexpr int NF = ShCount<DEG>::NF;
+    const float* base = shs + g * (int64_t)sh_coeffs * 3;
+    if (vec_ok) {
+        const float4* b4 = reinterpret_cast<const float4*>(base);
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            float4 v = __ldg(b4 + i);
+            c[4 * i + 0] = v.x; c[4 * i + 1] = v.y; c[4 * i + 2] = v.z; c[4 * i + 3] = v.w;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < NF; ++i) c[i] = __ldg(base + i);
+    }
+}
+
+template <int DEG>
+__global__ void __launch_bounds__(PROJ_THREADS)
+project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__ quats,
+                      const float* __restrict__ scales, const float* __restrict__ opacities,
+                      const float* __restrict__ shs, int sh_coeffs, bool vec_ok, int64_t N, Cam cam,
+                      int32_t* __restrict__ radii, float* __restrict__ splats,
+                      int32_t* __restrict__ tiles_per_gauss, int64_t* __restrict__ block_sums) {
+    int64_t g = (int64_t)blockIdx.x * PROJ_THREADS + threadIdx.x;
+    int ntiles = 0;
+    if (g < N) {
+        float px = __ldg(means + 3 * g), py = __ldg(means + 3 * g + 1), pz = __ldg(means + 3 * g + 2);
+        float4 q = __ldg(reinterpret_cast<const float4*>(quats) + g);
+        float sx = __ldg(scales + 3 * g), sy = __ldg(scales + 3 * g + 1), sz = __ldg(scales + 3 * g + 2);
+        float opac = __ldg(opacities + g);
+        Proj P;
+        int rx = 0, ry = 0;
+        bool ok = project_core(cam, px, py, pz, q, sx, sy, sz, P) && radius_and_cull(cam, P, opac, rx, ry);
+        float4 r0 = make_float4(0.f, 0.f, 0.f, 0.f), r1 = r0, r2 = r0;
+        if (ok) {
+            float col[3];
+            if (DEG >= 0) {
+                constexpr int D = DEG < 0 ? 0 : DEG;
+                constexpr int NB = ShCount<D>::NB;
+                float c[ShCount<D>::NV * 4];
+                load_sh<D>(shs, g, sh_coeffs, vec_ok, c);
+                float ux = px - cam.campos[0], uy = py - cam.campos[1], uz = pz - cam.campos[2];
+                float inv = rsqrtf(ux * ux + uy * uy + uz * uz);
+                float B[NB];
+                sh_basis<D>(ux * inv, uy * inv, uz * inv, B);
+                float r = 0.f, gg = 0.f, b = 0.f;
+#pragma unroll
+                for (int k = 0; k < NB; ++k) {
+                    r += B[k] * c[3 * k];
+                    gg += B[k] * c[3 * k + 1];
+                    b += B[k] * c[3 * k + 2];
+                }
+                col[0] = fmaxf(r + 0.5f, 0.f); col[1] = fmaxf(gg + 0.5f, 0.f); col[2] = fmaxf(b + 0.5f, 0.f);
+            } else {  // plain colours [N,3]
+                col[0] = __ldg(shs + 3 * g); col[1] = __ldg(shs + 3 * g + 1); col[2] = __ldg(shs + 3 * g + 2);
+            }
+            float inv_det = 1.f / P.det;
+            r0 = make_float4(P.mx, P.my, P.c * inv_det, -P.b * inv_det);
+            r1 = make_float4(P.a * inv_det, opac, col[0], col[1]);
+            r2 = make_float4(col[2], P.pcz, 0.f, 0.f);
+            // tile rectangle — same fp32 operations as the oracle's tile_bounds
+            float tile_x = P.mx / (float)TILE, tile_y = P.my / (float)TILE;
+            float trx = (float)rx / (float)TILE, try_ = (float)ry / (float)TILE;
+            float fw = (float)cam.tile_w, fh = (float)cam.tile_h;
+            int minx = (int)fminf(fmaxf(floorf(tile_x - trx), 0.f), fw);
+            int maxx = (int)fminf(fmaxf(ceilf(tile_x + trx), 0.f), fw);
+            int miny = (int)fminf(fmaxf(floorf(tile_y - try_), 0.f), fh);
+            int maxy = (int)fminf(fmaxf(ceilf(tile_y + try_), 0.f), fh);
+            ntiles = (maxy - miny) * (maxx - minx);
+        } else {
+            rx = ry = 0;
+        }
+        reinterpret_cast<int2*>(radii)[g] = make_int2(rx, ry);
+        float4* rec = reinterpret_cast<float4*>(splats) + 3 * g;
+        rec[0] = r0; rec[1] = r1; rec[2] = r2;
+        tiles_per_gauss[g] = ntiles;
+    }
+    // block sum of tile counts (feeds b200_bin_scan)
+    __shared__ int warp_tot[PROJ_THREADS / 32];
+    int v = ntiles;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) warp_tot[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int64_t tot = 0;
+#pragma unroll
+        for (int i = 0; i < PROJ_THREADS / 32; ++i) tot += warp_tot[i];
+        block_sums[blockIdx.x] = tot;
+    }
+}
+
+template <int DEG>
+__global__ void __launch_bounds__(PROJ_THREADS)
+project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__ quats,
+                      const float* __restrict__ scales, const float* __restrict__ opacities,
+                      const float* __restrict__ shs, int sh_coeffs, bool vec_ok, int64_t N, Cam cam,
+                      const int32_t* __restrict__ radii, const float* __restrict__ v_splats,
+                      float* __restrict__ v_means, float* __restrict__ v_quats, float* __restrict__ v_scales,
+                      float* __restrict__ v_opacities, float* __restrict__ v_shs) {
+    int64_t g = (int64_t)blockIdx.x * PROJ_THREADS + threadIdx.x;
+    if (g >= N) return;
+    int2 rad = __ldg(reinterpret_cast<const int2*>(radii) + g);
+    bool vis = rad.x > 0 && rad.y > 0;
+    float vm[3] = {0.f, 0.f, 0.f}, vq[4] = {0.f, 0.f, 0.f, 0.f}, vs[3] = {0.f, 0.f, 0.f}, vo = 0.f;
+    const int ncoef_f = sh_coeffs * 3;
+    float* vsh = (DEG >= 0) ? v_shs + g * (int64_t)ncoef_f : v_shs + 3 * g;
+
+    if (!vis) {
+        if (DEG >= 0) {
+            if (vec_ok) {
+                float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int i = 0; i < ncoef_f / 4; ++i) reinterpret_cast<float4*>(vsh)[i] = z4;
+            } else {
+                for (int i = 0; i < ncoef_f; ++i) vsh[i] = 0.f;
+            }
+        } else {
+            vsh[0] = vsh[1] = vsh[2] = 0.f;
+        }
+    } else {
+        float px = __ldg(means + 3 * g), py = __ldg(means + 3 * g + 1), pz = __ldg(means + 3 * g + 2);
+        float4 q = __ldg(reinterpret_cast<const float4*>(quats) + g);
+        float sx = __ldg(scales + 3 * g), sy = __ldg(scales + 3 * g + 1), sz = __ldg(scales + 3 * g + 2);
+        const float4* vrec = reinterpret_cast<const float4*>(v_splats) + 3 * g;
+        float4 g0 = __ldg(vrec), g1 = __ldg(vrec + 1), g2 = __ldg(vrec + 2);
+        float v_mx = g0.x, v_my = g0.y, v_A = g0.z, v_B = g0.w, v_C = g1.x;
+        vo = g1.y;
+        float v_col[3] = {g1.z, g1.w, g2.x};
+        float v_depth = g2.y;
+        Proj P;
+        project_core(cam, px, py, pz, q, sx, sy, sz, P);
+
+        // ---- SH colour VJP (A.2) ----
+        if (DEG >= 0) {
+            constexpr int D = DEG < 0 ? 0 : DEG;
+            constexpr int NB = ShCount<D>::NB;
+            float c[ShCount<D>::NV * 4];
+            load_sh<D>(shs, g, sh_coeffs, vec_ok, c);
+            float ux = px - cam.campos[0], uy = py - cam.campos[1], uz = pz - cam.campos[2];
+            float inv = rsqrtf(ux * ux + uy * uy + uz * uz);
+            float x = ux * inv, y = uy * inv, z = uz * inv;
+            float B[NB];
+            sh_basis<D>(x, y, z, B);
+            float rgb[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+            for (int k = 0; k < NB; ++k) {
+                rgb[0] += B[k] * c[3 * k]; rgb[1] += B[k] * c[3 * k + 1]; rgb[2] += B[k] * c[3 * k + 2];
+            }
+            float vr[3];
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch) vr[ch] = (rgb[ch] + 0.5f >= 0.f) ? v_col[ch] : 0.f;
+            // coefficient gradients
+            float out[48];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch) out[3 * k + ch] = (k < NB) ? B[k] * vr[ch] : 0.f;
+            }
+            if (vec_ok && sh_coeffs == 16) {
+#pragma unroll
+                for (int i = 0; i < 12; ++i)
+                    reinterpret_cast<float4*>(vsh)[i] = make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]);
+            } else {
+                for (int i = 0; i < ncoef_f; ++i) vsh[i] = (i < 48) ? out[i] : 0.f;
+            }
+            // direction gradient
+            float gk[NB];
+#pragma unroll
+            for (int k = 0; k < NB; ++k) gk[k] = c[3 * k] * vr[0] + c[3 * k + 1] * vr[1] + c[3 * k + 2] * vr[2];
+            float vdx = 0.f, vdy = 0.f, vdz = 0.f;
+            if (D >= 1) {
+                vdy += -SH_C1 * gk[1]; vdz += SH_C1 * gk[2]; vdx += -SH_C1 * gk[3];
+            }
+            if (D >= 2) {
+                vdx += SH_C2A * 2.f * y * gk[4]; vdy += SH_C2A * 2.f * x * gk[4];
+                vdy += -SH_C2B * z * gk[5]; vdz += -SH_C2B * y * gk[5];
+                vdz += 2.f * SH_C2C * z * gk[6];
+                vdx += -SH_C2B * z * gk[7]; vdz += -SH_C2B * x * gk[7];
+                vdx += SH_C2A * 2.f * x * gk[8]; vdy += -SH_C2A * 2.f * y * gk[8];
+            }
+            if (D >= 3) {
+                float z2 = z * z, fT0C = -SH_C3C * z2 + SH_C3D, x2my2 = x * x - y * y;
+                vdx += -SH_C3A * 6.f * x * y * gk[9]; vdy += -SH_C3A * 3.f * x2my2 * gk[9];
+                vdx += 2.f * SH_C3B * y * z * gk[10]; vdy += 2.f * SH_C3B * x * z * gk[10]; vdz += 2.f * SH_C3B * x * y * gk[10];
+                vdy += fT0C * gk[11]; vdz += -2.f * SH_C3C * z * y * gk[11];
+                vdz += (3.f * SH_C3E * z2 - SH_C3F) * gk[12];
+                vdx += fT0C * gk[13]; vdz += -2.f * SH_C3C * z * x * gk[13];
+                vdx += SH_C3B * 2.f * x * z * gk[14]; vdy += -SH_C3B * 2.f * y * z * gk[14]; vdz += SH_C3B * x2my2 * gk[14];
+                vdx += -SH_C3A * 3.f * x2my2 * gk[15]; vdy += SH_C3A * 6.f * x * y * gk[15];
+            }
+            float dot = x * vdx + y * vdy + z * vdz;
+            vm[0] += (vdx - x * dot) * inv; vm[1] += (vdy - y * dot) * inv; vm[2] += (vdz - z * dot) * inv;
+        } else {
+            vsh[0] = v_col[0]; vsh[1] = v_col[1]; vsh[2] = v_col[2];
+        }
+
+        // ---- conic -> 2-D covariance (A.6) ----
+        float inv_det = 1.f / P.det;
+        float A = P.c * inv_det, Bc = -P.b * inv_det, C = P.a * inv_det;
+        float hB = 0.5f * v_B;
+        float xv00 = A * v_A + Bc * hB, xv01 = A * hB + Bc * v_C;
+        float xv10 = Bc * v_A + C * hB, xv11 = Bc * hB + C * v_C;
+        float G00 = -(xv00 * A + xv01 * Bc), G01 = -(xv00 * Bc + xv01 * C);
+        float G10 = -(xv10 * A + xv11 * Bc), G11 = -(xv10 * Bc + xv11 * C);
+        float Gs = 0.5f * (G01 + G10);
+        // S2 = T T^T  ->  v_T = 2 G T
+        float vT[6];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            vT[j] = 2.f * (G00 * P.T[j] + Gs * P.T[3 + j]);
+            vT[3 + j] = 2.f * (Gs * P.T[j] + G11 * P.T[3 + j]);
+        }
+        // T = J Wm: v_J = v_T Wm^T (only 4 live entries), v_Wm = J^T v_T
+        float vJ00 = 0.f, vJ02 = 0.f, vJ11 = 0.f, vJ12 = 0.f;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            vJ00 += vT[j] * P.Wm[j];
+            vJ02 += vT[j] * P.Wm[6 + j];
+            vJ11 += vT[3 + j] * P.Wm[3 + j];
+            vJ12 += vT[3 + j] * P.Wm[6 + j];
+        }
+        float vW[9];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            vW[j] = P.J00 * vT[j];
+            vW[3 + j] = P.J11 * vT[3 + j];
+            vW[6 + j] = P.J02 * vT[j] + P.J12 * vT[3 + j];
+        }
+        // Wm = R Rq diag(s): v_(Rq diag s) = R^T v_Wm
+        const float* R = cam.R;
+        const float s[3] = {sx, sy, sz};
+        float vRq[9];
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                float vMij = R[0 * 3 + i] * vW[0 * 3 + j] + R[1 * 3 + i] * vW[1 * 3 + j] + R[2 * 3 + i] * vW[2 * 3 + j];
+                vs[j] += P.Rq[i * 3 + j] * vMij;
+                vRq[i * 3 + j] = vMij * s[j];
+            }
+        {
+            float w = P.qn[0], x = P.qn[1], y = P.qn[2], z = P.qn[3];
+            float vw = 2.f * (-z * vRq[1] + y * vRq[2] + z * vRq[3] - x * vRq[5] - y * vRq[6] + x * vRq[7]);
+            float vx = 2.f * (y * vRq[1] + z * vRq[2] + y * vRq[3] - 2.f * x * vRq[4] - w * vRq[5] + z * vRq[6] + w * vRq[7] - 2.f * x * vRq[8]);
+            float vy = 2.f * (-2.f * y * vRq[0] + x * vRq[1] + w * vRq[2] + x * vRq[3] + z * vRq[5] - w * vRq[6] + z * vRq[7] - 2.f * y * vRq[8]);
+            float vz = 2.f * (-2.f * z * vRq[0] - w * vRq[1] + x * vRq[2] + w * vRq[3] - 2.f * z * vRq[4] + y * vRq[5] + x * vRq[6] + y * vRq[7]);
+            float dot = w * vw + x * vx + y * vy + z * vz;
+            vq[0] = (vw - w * dot) * P.inv_norm; vq[1] = (vx - x * dot) * P.inv_norm;
+            vq[2] = (vy - y * dot) * P.inv_norm; vq[3] = (vz - z * dot) * P.inv_norm;
+        }
+        // ---- perspective projection VJP: J, mean2d, depth -> camera-space mean ----
+        float rz = P.rz, rz2 = rz * rz, rz3 = rz2 * rz;
+        float vpx = cam.fx * rz * v_mx;
+        float vpy = cam.fy * rz * v_my;
+        float vpz = -(cam.fx * P.pcx * v_mx + cam.fy * P.pcy * v_my) * rz2 + v_depth;
+        vpz += -cam.fx * rz2 * vJ00 - cam.fy * rz2 * vJ11;
+        if (!P.clamp_x) { vpx += -cam.fx * rz2 * vJ02; vpz += 2.f * cam.fx * P.tx * rz3 * vJ02; }
+        else            { vpz += cam.fx * P.tx * rz3 * vJ02; }
+        if (!P.clamp_y) { vpy += -cam.fy * rz2 * vJ12; vpz += 2.f * cam.fy * P.ty * rz3 * vJ12; }
+        else            { vpz += cam.fy * P.ty * rz3 * vJ12; }
+        vm[0] += R[0] * vpx + R[3] * vpy + R[6] * vpz;
+        vm[1] += R[1] * vpx + R[4] * vpy + R[7] * vpz;
+        vm[2] += R[2] * vpx + R[5] * vpy + R[8] * vpz;
+    }
+    v_means[3 * g] = vm[0]; v_means[3 * g + 1] = vm[1]; v_means[3 * g + 2] = vm[2];
+    reinterpret_cast<float4*>(v_quats)[g] = make_float4(vq[0], vq[1], vq[2], vq[3]);
+    v_scales[3 * g] = vs[0]; v_scales[3 * g + 1] = vs[1]; v_scales[3 * g + 2] = vs[2];
+    v_opacities[g] = vo;
+}
+
+}  // namespace
+
+extern "C" int64_t b200_project_blocks(int64_t N) { return (N + PROJ_THREADS - 1) / PROJ_THREADS; }
+
+static bool sh_args_ok(int sh_coeffs, int sh_degree) {
+    if (sh_degree < 0) return true;
+    return sh_degree <= 3 && (sh_degree + 1) * (sh_degree + 1) <= sh_coeffs;
+}
+
+extern "C" int b200_project_sh_fwd(const float* means, const float* quats, const float* scales,
+                                   const float* opacities, const float* shs, int sh_coeffs, int sh_degree,
+                                   int64_t N, const float* cam_host, int width, int height, int32_t* radii,
+                                   float* splats, int32_t* tiles_per_gauss, int64_t* block_sums, void* stream) {
+    B200_REQUIRE(N >= 0 && width > 0 && height > 0, "bad sizes");
+    B200_REQUIRE(sh_args_ok(sh_coeffs, sh_degree), "sh_degree/sh_coeffs mismatch");
+    if (N == 0) return B200_OK;
+    B200_REQUIRE(means && quats && scales && opacities && shs && cam_host && radii && splats && tiles_per_gauss && block_sums, "null pointer");
+    B200_REQUIRE(((uintptr_t)quats & 15) == 0 && ((uintptr_t)splats & 15) == 0 && ((uintptr_t)radii & 7) == 0, "misaligned pointer");
+    Cam cam = b200_make_cam(cam_host, width, height);
+    bool vec_ok = sh_degree >= 0 && ((sh_coeffs * 12) % 16 == 0) && (((uintptr_t)shs & 15) == 0);
+    dim3 grid((unsigned)b200_project_blocks(N)), block(PROJ_THREADS);
+    cudaStream_t st = (cudaStream_t)stream;
+#define LAUNCH(D) project_sh_fwd_kernel<D><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, cam, radii, splats, tiles_per_gauss, block_sums)
+    switch (sh_degree) {
+        case 0: LAUNCH(0); break;
+        case 1: LAUNCH(1); break;
+        case 2: LAUNCH(2); break;
+        case 3: LAUNCH(3); break;
+        default: LAUNCH(-1); break;
+    }
+#undef LAUNCH
+    return b200_check_launch("project_sh_fwd");
+}
+
+extern "C" int b200_project_sh_bwd(const float* means, const float* quats, const float* scales,
+                                   const float* opacities, const float* shs, int sh_coeffs, int sh_degree,
+                                   int64_t N, const float* cam_host, int width, int height, const int32_t* radii,
+                                   const float* v_splats, float* v_means, float* v_quats, float* v_scales,
+                                   float* v_opacities, float* v_shs, void* stream) {
+    B200_REQUIRE(N >= 0 && width > 0 && height > 0, "bad sizes");
+    B200_REQUIRE(sh_args_ok(sh_coeffs, sh_degree), "sh_degree/sh_coeffs mismatch");
+    if (N == 0) return B200_OK;
+    B200_REQUIRE(means && quats && scales && opacities && shs && cam_host && radii && v_splats && v_means && v_quats && v_scales && v_opacities && v_shs, "null pointer");
+    B200_REQUIRE(((uintptr_t)quats & 15) == 0 && ((uintptr_t)v_splats & 15) == 0 && ((uintptr_t)v_quats & 15) == 0 && ((uintptr_t)radii & 7) == 0, "misaligned pointer");
+    Cam cam = b200_make_cam(cam_host, width, height);
+    bool vec_ok = sh_degree >= 0 && ((sh_coeffs * 12) % 16 == 0) && (((uintptr_t)shs & 15) == 0) && (((uintptr_t)v_shs & 15) == 0);
+    dim3 grid((unsigned)b200_project_blocks(N)), block(PROJ_THREADS);
+    cudaStream_t st = (cudaStream_t)stream;
+#define LAUNCH(D) project_sh_bwd_kernel<D><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, cam, radii, v_splats, v_means, v_quats, v_scales, v_opacities, v_shs)
+    switch (sh_degree) {
+        case 0: LAUNCH(0); break;
+        case 1: LAUNCH(1); break;
+        case 2: LAUNCH(2); break;
+        case 3: LAUNCH(3); break;
+        default: LAUNCH(-1); break;
+    }
+#undef LAUNCH
+    return b200_check_launch("project_sh_bwd");
+}

@@ -1,0 +1,90 @@
+"""Multi-GPU data path: camera views sharded over ranks, Gaussians replicated, ONE all-reduce of a flat
+gradient buffer per step (BASELINE.json north_star).
+
+The reference has no distributed code; the contract here is "the reduced gradient equals
+the single-process gradient of the mean loss over the same global batch of views"
+(src/training/trainer.py:458-500 sums per-view losses and divides by the batch size).  One process
+per GPU, ``torch.distributed`` (NCCL over NVLink on the GPU box, gloo in the CPU tests).
+"""
+from __future__ import annotations
+
+from typing import Callable, Iterable, List, Sequence
+
+import torch
+import torch.distributed as dist
+
+
+def shard_views(n_views: int, rank: int, world_size: int) -> List[int]:
+    """Round-robin view indices of this rank (balanced to within one view for any n_views)."""
+    if not (0 <= rank < world_size):
+        raise ValueError(f"rank {rank} outside world of {world_size}")
+    return list(range(rank, n_views, world_size))
+
+
+def _flat_numel(params: Sequence[torch.Tensor]) -> int:
+    return sum(p.numel() for p in params)
+
+
+def allreduce_gradients(params: Iterable[torch.Tensor], n_global_views: int, group=None,
+                        flat: torch.Tensor = None) -> torch.Tensor:
+    """Sum-all-reduce every ``p.grad`` through one contiguous fp32 buffer (59*N floats for the six
+    Gaussian attributes), then scale by 1/n_global_views so the result is the gradient of the MEAN
+    per-view loss.  Local gradients must be those of the SUM of the rank's per-view losses.
+    Returns the flat buffer (reusable via ``flat=``)."""
+    params = [p for p in params if p.requires_grad]
+    n = _flat_numel(params)
+    dev = params[0].device
+    if flat is None or flat.numel() != n or flat.device != dev:
+        flat = torch.empty(n, dtype=torch.float32, device=dev)
+    off = 0
+    for p in params:
+        k = p.numel()
+        if p.grad is None:
+            flat[off:off + k].zero_()
+        else:
+            flat[off:off + k].copy_(p.grad.reshape(-1))
+        off += k
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    flat.mul_(1.0 / float(n_global_views))
+    off = 0
+    for p in params:
+        k = p.numel()
+        g = flat[off:off + k].view_as(p)
+        if p.grad is None:
+            p.grad = g.clone()
+        else:
+            p.grad.copy_(g)
+        off += k
+    return flat
+
+
+class ViewShardedStep:
+    """One optimisation step over a global batch of views, this rank rendering only its shard.
+
+    ``render_loss(view) -> scalar loss`` must build the autograd graph from ``params``.  After
+    ``__call__`` every rank holds identical ``p.grad`` = d(mean_v loss_v)/dp, so identical optimiser
+    steps keep the replicas bit-identical without a parameter broadcast.  The densification statistic
+    is a norm of the REDUCED gradient and therefore must be taken after this call."""
+
+    def __init__(self, params: Sequence[torch.Tensor], group=None):
+        self.params = list(params)
+        self.group = group
+        self._flat = None
+
+    def __call__(self, views: Sequence, render_loss: Callable[[object], torch.Tensor]) -> float:
+        world = dist.get_world_size(self.group) if dist.is_initialized() else 1
+        rank = dist.get_rank(self.group) if dist.is_initialized() else 0
+        for p in self.params:
+            p.grad = None
+        local_sum = 0.0
+        mine = shard_views(len(views), rank, world)
+        for i in mine:
+            loss = render_loss(views[i])
+            loss.backward()
+            local_sum += float(loss.detach())
+        self._flat = allreduce_gradients(self.params, len(views), self.group, self._flat)
+        t = torch.tensor([local_sum], dtype=torch.float64, device=self.params[0].device)
+        if world > 1:
+            dist.all_reduce(t, group=self.group)
+        return float(t.item()) / len(views)

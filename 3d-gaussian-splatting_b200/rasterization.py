@@ -1,0 +1,282 @@
+"""Host side of the rasterizer: stage orchestration over the C ABI and the autograd bridge.
+
+``rasterization(...)`` mirrors the call the reference makes into gsplat 1.5.3
+(src/backends/gsplat_backend.py:83-97 and :168-182): same argument names, same return triple
+``(renders[C,H,W,CH], alphas[C,H,W,1], meta)`` and the same ``meta`` keys the reference reads
+(``means2d``, ``radii`` — gsplat_backend.py:204-208) plus gsplat's binning keys used by the parity
+tests (``tiles_per_gauss, isect_ids, flatten_ids, isect_offsets``).
+
+PyTorch is plumbing only here (device memory, current stream, autograd graph); every stage is a
+hand-written sm_100a kernel reached through ``libb200splat.so``.  No CPU path exists.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import lib, check
+
+_MODES = {"RGB": _lib.CH_RGB, "D": _lib.CH_D, "ED": _lib.CH_D, "RGB+D": _lib.CH_RGBD, "RGB+ED": _lib.CH_RGBD}
+_NCH = {_lib.CH_RGB: 3, _lib.CH_D: 1, _lib.CH_RGBD: 4}
+
+
+class _stage:
+    """Brackets one stage with CUDA events when bench.py installed a recorder in ``_lib.stage_timer``."""
+
+    __slots__ = ("name",)
+
+    def __init__(self, name: str):
+        self.name = name
+
+    def __enter__(self):
+        if _lib.stage_timer is not None:
+            _lib.stage_timer.begin(self.name)
+
+    def __exit__(self, *exc):
+        if _lib.stage_timer is not None:
+            _lib.stage_timer.end(self.name)
+        return False
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _require_cuda(*tensors: torch.Tensor) -> torch.device:
+    dev = tensors[0].device
+    for t in tensors:
+        if t.device.type != "cuda":
+            raise RuntimeError(
+                "b200 rasterizer: all inputs must be CUDA tensors (there is no CPU fallback); got "
+                f"{t.device}"
+            )
+        if t.device != dev:
+            raise RuntimeError("b200 rasterizer: inputs live on different devices")
+    return dev
+
+
+def make_cam(viewmat: torch.Tensor, K: torch.Tensor, near_plane: float = 0.01, far_plane: float = 1e10,
+             eps2d: float = 0.3, radius_clip: float = 0.0):
+    """24-float host camera block of include/b200splat.h (B200_CAM_FLOATS)."""
+    vm = viewmat.detach().to(dtype=torch.float32, device="cpu").reshape(16).tolist()
+    Kc = K.detach().to(dtype=torch.float32, device="cpu")
+    vals = vm + [float(Kc[0, 0]), float(Kc[1, 1]), float(Kc[0, 2]), float(Kc[1, 2]),
+                 float(near_plane), float(far_plane), float(eps2d), float(radius_clip)]
+    return (C.c_float * _lib.CAM_FLOATS)(*vals)
+
+
+def tile_n_bits(tile_w: int, tile_h: int) -> int:
+    return int(math.floor(math.log2(tile_w * tile_h))) + 1
+
+
+def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional[int], cam, width: int,
+                    height: int, keep_unsorted: bool = False) -> Dict[str, torch.Tensor]:
+    """Stages 1-2 (projection+SH, tile binning, radix sort, tile ranges).  One host sync (reads M)."""
+    dev = means.device
+    N = means.shape[0]
+    tile_w = (width + _lib.TILE - 1) // _lib.TILE
+    tile_h = (height + _lib.TILE - 1) // _lib.TILE
+    n_tiles = tile_w * tile_h
+    st = _stream()
+    if sh_degree is None:
+        sh_coeffs, deg = 1, -1
+    else:
+        sh_coeffs, deg = colors.shape[1], int(sh_degree)
+    radii = torch.empty(N, 2, dtype=torch.int32, device=dev)
+    splats = torch.empty(N, _lib.SPLAT_FLOATS, dtype=torch.float32, device=dev)
+    tiles_per_gauss = torch.empty(N, dtype=torch.int32, device=dev)
+    nblocks = int(lib.b200_project_blocks(N))
+    block_sums = torch.empty(max(nblocks, 1), dtype=torch.int64, device=dev)
+    block_offsets = torch.empty(max(nblocks, 1), dtype=torch.int64, device=dev)
+    total = torch.zeros(1, dtype=torch.int64, device=dev)
+    with _stage("project_sh_fwd"):
+        check(lib.b200_project_sh_fwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors),
+                                      sh_coeffs, deg, N, cam, width, height, _ptr(radii), _ptr(splats),
+                                      _ptr(tiles_per_gauss), _ptr(block_sums), st), "b200_project_sh_fwd")
+    with _stage("bin_scan"):
+        check(lib.b200_bin_scan(_ptr(block_sums), nblocks, _ptr(block_offsets), _ptr(total), st), "b200_bin_scan")
+    M = int(total.item())  # the one device->host sync of the forward pass (sizes the key buffers)
+    keys_a = torch.empty(max(M, 1), dtype=torch.int64, device=dev)
+    vals_a = torch.empty(max(M, 1), dtype=torch.int32, device=dev)
+    with _stage("bin_emit"):
+        check(lib.b200_bin_emit(_ptr(splats), _ptr(radii), _ptr(tiles_per_gauss), _ptr(block_offsets), N, width,
+                                height, M, _ptr(keys_a), _ptr(vals_a), None, st), "b200_bin_emit")
+    out = dict(radii=radii, splats=splats, tiles_per_gauss=tiles_per_gauss, M=M, tile_w=tile_w, tile_h=tile_h)
+    if keep_unsorted:
+        out["isect_ids_unsorted"] = keys_a[:M].clone()
+        out["flatten_ids_unsorted"] = vals_a[:M].clone()
+    keys_b = torch.empty_like(keys_a)
+    vals_b = torch.empty_like(vals_a)
+    sbytes = int(lib.b200_sort_scratch_bytes(M))
+    scratch = torch.empty(max(sbytes, 256), dtype=torch.uint8, device=dev)
+    in_b = C.c_int(0)
+    end_bit = 32 + tile_n_bits(tile_w, tile_h)
+    with _stage("sort_pairs"):
+        check(lib.b200_sort_pairs(_ptr(keys_a), _ptr(vals_a), _ptr(keys_b), _ptr(vals_b), M, end_bit,
+                                  _ptr(scratch), scratch.numel(), C.byref(in_b), st), "b200_sort_pairs",
+              kernels=(2 + (end_bit + 7) // 8) if M > 0 else 0)
+    keys_s, vals_s = (keys_b, vals_b) if in_b.value else (keys_a, vals_a)
+    offsets = torch.empty(n_tiles, dtype=torch.int32, device=dev)
+    with _stage("tile_ranges"):
+        check(lib.b200_tile_ranges(_ptr(keys_s), M, n_tiles, _ptr(offsets), st), "b200_tile_ranges")
+    out.update(isect_ids=keys_s[:M], flatten_ids=vals_s[:M], isect_offsets=offsets.view(tile_h, tile_w))
+    return out
+
+
+class RasterizeSplats(torch.autograd.Function):
+    """forward = stages 1-3, backward = stages 4a-4b (gsplat's autograd of rasterization())."""
+
+    @staticmethod
+    @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
+    def forward(ctx, means, quats, scales, opacities, colors, cam, width, height, sh_degree, chset, background):
+        _require_cuda(means, quats, scales, opacities, colors)
+        means, quats, scales = means.contiguous(), quats.contiguous(), scales.contiguous()
+        opacities, colors = opacities.contiguous(), colors.contiguous()
+        dev = means.device
+        with torch.cuda.device(dev):
+            b = project_and_bin(means, quats, scales, opacities, colors, sh_degree, cam, width, height)
+            nch = _NCH[chset]
+            render = torch.empty(height, width, nch, dtype=torch.float32, device=dev)
+            alpha = torch.empty(height, width, 1, dtype=torch.float32, device=dev)
+            last_ids = torch.empty(height, width, dtype=torch.int32, device=dev)
+            bg = (C.c_float * 4)(*([float(x) for x in background] + [0.0] * (4 - len(background))))
+            with _stage("raster_fwd"):
+                check(lib.b200_raster_fwd(_ptr(b["splats"]), _ptr(b["flatten_ids"]), _ptr(b["isect_offsets"]), b["M"],
+                                          width, height, chset, bg, _ptr(render), _ptr(alpha), _ptr(last_ids),
+                                          _stream()), "b200_raster_fwd")
+        ctx.save_for_backward(means, quats, scales, opacities, colors, b["radii"], b["splats"], b["flatten_ids"],
+                              b["isect_offsets"], alpha, last_ids)
+        ctx.cfg = (cam, width, height, sh_degree, chset, bg, b["M"])
+        ctx.mark_non_differentiable(b["radii"], b["splats"], b["tiles_per_gauss"], b["isect_ids"],
+                                    b["flatten_ids"], b["isect_offsets"], last_ids)
+        return (render, alpha, b["radii"], b["splats"], b["tiles_per_gauss"], b["isect_ids"], b["flatten_ids"],
+                b["isect_offsets"], last_ids)
+
+    @staticmethod
+    @torch.amp.custom_bwd(device_type="cuda")
+    def backward(ctx, v_render, v_alpha, *_unused):
+        means, quats, scales, opacities, colors, radii, splats, flatten_ids, offsets, alpha, last_ids = ctx.saved_tensors
+        cam, width, height, sh_degree, chset, bg, M = ctx.cfg
+        dev = means.device
+        N = means.shape[0]
+        nch = _NCH[chset]
+        if v_render is None:
+            v_render = torch.zeros(height, width, nch, dtype=torch.float32, device=dev)
+        v_render = v_render.to(torch.float32).contiguous()
+        if v_alpha is not None:
+            v_alpha = v_alpha.to(torch.float32).contiguous()
+        with torch.cuda.device(dev):
+            st = _stream()
+            v_splats = torch.zeros(N, _lib.SPLAT_FLOATS, dtype=torch.float32, device=dev)
+            with _stage("raster_bwd"):
+                check(lib.b200_raster_bwd(_ptr(splats), _ptr(flatten_ids), _ptr(offsets), M, width, height, chset, bg,
+                                          _ptr(alpha), _ptr(last_ids), _ptr(v_render), _ptr(v_alpha), _ptr(v_splats),
+                                          st), "b200_raster_bwd")
+            v_means = torch.empty_like(means)
+            v_quats = torch.empty_like(quats)
+            v_scales = torch.empty_like(scales)
+            v_opac = torch.empty_like(opacities)
+            v_colors = torch.empty_like(colors)
+            if sh_degree is None:
+                sh_coeffs, deg = 1, -1
+            else:
+                sh_coeffs, deg = colors.shape[1], int(sh_degree)
+            with _stage("project_sh_bwd"):
+                check(lib.b200_project_sh_bwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors),
+                                              sh_coeffs, deg, N, cam, width, height, _ptr(radii), _ptr(v_splats),
+                                              _ptr(v_means), _ptr(v_quats), _ptr(v_scales), _ptr(v_opac),
+                                              _ptr(v_colors), st), "b200_project_sh_bwd")
+        return v_means, v_quats, v_scales, v_opac, v_colors, None, None, None, None, None, None
+
+
+def _render_one(means, quats, scales, opacities, colors, viewmat, K, width, height, sh_degree, render_mode,
+                background, near_plane, far_plane, eps2d, radius_clip):
+    chset = _MODES[render_mode]
+    nch = _NCH[chset]
+    if background is None:
+        bg = [0.0] * nch
+    else:
+        bgl = [float(x) for x in background.detach().reshape(-1).to("cpu").tolist()]
+        if chset == _lib.CH_RGB:
+            bg = bgl[:3]
+        elif chset == _lib.CH_D:
+            bg = [0.0]
+        else:
+            bg = bgl[:3] + [0.0]  # depth channel composites over 0
+    cam = make_cam(viewmat, K, near_plane, far_plane, eps2d, radius_clip)
+    out = RasterizeSplats.apply(means, quats, scales, opacities, colors, cam, int(width), int(height), sh_degree,
+                                chset, bg)
+    render, alpha, radii, splats, tiles_per_gauss, isect_ids, flatten_ids, offsets, last_ids = out
+    if render_mode in ("ED", "RGB+ED"):
+        render = torch.cat([render[..., :-1], render[..., -1:] / alpha.clamp(min=1e-10)], dim=-1)
+    return render, alpha, dict(radii=radii, splats=splats, tiles_per_gauss=tiles_per_gauss, isect_ids=isect_ids,
+                               flatten_ids=flatten_ids, isect_offsets=offsets, last_ids=last_ids)
+
+
+def rasterization(means: torch.Tensor, quats: torch.Tensor, scales: torch.Tensor, opacities: torch.Tensor,
+                  colors: torch.Tensor, viewmats: torch.Tensor, Ks: torch.Tensor, width: int, height: int,
+                  near_plane: float = 0.01, far_plane: float = 1e10, radius_clip: float = 0.0,
+                  eps2d: float = 0.3, sh_degree: Optional[int] = None, packed: bool = False,
+                  tile_size: int = 16, backgrounds: Optional[torch.Tensor] = None, render_mode: str = "RGB",
+                  **unsupported) -> Tuple[torch.Tensor, torch.Tensor, Dict]:
+    """Drop-in for ``gsplat.rasterization`` with the argument set the reference uses.
+
+    means[N,3] quats[N,4](wxyz) scales[N,3] opacities[N] colors=[N,K,3] SH coefficients (``sh_degree``
+    given) or [N,3] colours; viewmats[C,4,4] world->camera, Ks[C,3,3] pixel intrinsics.  Returns
+    ``(renders[C,H,W,CH], alphas[C,H,W,1], meta)``.
+    """
+    if render_mode not in _MODES:
+        raise ValueError(f"render_mode must be one of {sorted(_MODES)}, got {render_mode!r}")
+    if packed:
+        raise NotImplementedError("packed=True is not used by the reference (gsplat_backend.py:178)")
+    if tile_size != _lib.TILE:
+        raise NotImplementedError("tile_size is fixed at 16 (gsplat default, the only value the reference uses)")
+    for k, v in unsupported.items():
+        if v not in (None, False, "classic", "pinhole"):
+            raise NotImplementedError(f"rasterization(): argument {k}={v!r} is outside the reference's call")
+    _require_cuda(means, quats, scales, opacities, colors, viewmats, Ks)
+    if opacities.dim() == 2:
+        opacities = opacities.squeeze(-1)
+    if viewmats.dim() == 2:
+        viewmats, Ks = viewmats[None], Ks[None]
+    Ccam = viewmats.shape[0]
+    renders, alphas, metas = [], [], []
+    for c in range(Ccam):
+        bg = None if backgrounds is None else (backgrounds[c] if backgrounds.dim() == 2 else backgrounds)
+        r, a, m = _render_one(means, quats, scales, opacities, colors, viewmats[c], Ks[c], width, height, sh_degree,
+                              render_mode, bg, near_plane, far_plane, eps2d, radius_clip)
+        renders.append(r)
+        alphas.append(a)
+        metas.append(m)
+    tile_w = (width + _lib.TILE - 1) // _lib.TILE
+    tile_h = (height + _lib.TILE - 1) // _lib.TILE
+    def _stk(key):  # C == 1 (the reference's only case) stays a zero-copy view
+        return metas[0][key][None] if Ccam == 1 else torch.stack([m[key] for m in metas])
+
+    sp = _stk("splats")
+    meta = {
+        "radii": _stk("radii"),
+        "means2d": sp[..., 0:2],
+        "conics": sp[..., 2:5],
+        "depths": sp[..., 9],
+        "colors": sp[..., 6:9],
+        "opacities": opacities[None].expand(Ccam, -1),
+        "tiles_per_gauss": _stk("tiles_per_gauss"),
+        "isect_ids": metas[0]["isect_ids"] if Ccam == 1 else [m["isect_ids"] for m in metas],
+        "flatten_ids": metas[0]["flatten_ids"] if Ccam == 1 else [m["flatten_ids"] for m in metas],
+        "isect_offsets": _stk("isect_offsets"),
+        "last_ids": _stk("last_ids"),
+        "tile_width": tile_w, "tile_height": tile_h, "tile_size": _lib.TILE,
+        "width": width, "height": height, "n_cameras": Ccam,
+    }
+    if Ccam == 1:
+        return renders[0][None], alphas[0][None], meta
+    return torch.stack(renders), torch.stack(alphas), meta

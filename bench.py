@@ -1,0 +1,373 @@
+#!/usr/bin/env python
+"""bench.py — fwd+bwd Mpix/s of the rasterizer hot path (BASELINE.json metric) on synthetic scenes.
+
+    python bench.py --gpus N --steps K --warmup W            # B200 arm (this repo's CUDA path)
+    python bench.py --impl reference --gpus N --steps K ...   # CPU arm: oracle/_cpu (C/OpenMP port) on host cores
+
+A "step" = every rank renders `views_per_rank` 1920x1080 views of the replicated 1 M-Gaussian SH-3 scene
+forward + backward (gradients w.r.t. all five activated tensors accumulate), and, for N>1, ONE NCCL
+all-reduce of the flat gradient buffer.  value = all ranks' pixels / max-over-ranks device time.
+Prints ONE JSON line on rank 0 (keys: see DESIGN.md "Measurement").
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+CONFIGS = {
+    # name: (N gaussians, W, H, sh_degree)
+    "A": (1_000_000, 1920, 1080, 3),   # BASELINE.json configs[1] — the configuration the metric is quoted on
+    "C": (6_000_000, 3840, 2160, 3),   # configs[3]
+    "B": (3_000_000, 1920, 1080, 3),   # configs[2] (per-rank view shard of the 64-camera set)
+    "tiny": (20_000, 320, 192, 3),
+}
+METRIC = "fwd+bwd Mpix/s (1M gaussians SH3, 1920x1080)"
+
+
+def _peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        super().__init__(daemon=True)
+        self.gpu = gpu_index
+        self.samples = []
+        self.stop_flag = threading.Event()
+
+    def run(self):
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                                      str(self.gpu)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self.stop_flag.wait(0.2)
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            try:
+                sm.append(float(s[1]))
+                mx.append(float(s[2]))
+                for n, v in zip(names, s[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+class StageTimer:
+    """CUDA-event recorder for the per-stage hooks in the package (events on the launching stream)."""
+
+    def __init__(self, torch):
+        self.torch = torch
+        self.open = {}
+        self.pairs = {}
+        self.enabled = False
+
+    def begin(self, name):
+        if not self.enabled:
+            return
+        e = self.torch.cuda.Event(enable_timing=True)
+        e.record()
+        self.open[name] = e
+
+    def end(self, name):
+        if not self.enabled:
+            return
+        e = self.torch.cuda.Event(enable_timing=True)
+        e.record()
+        self.pairs.setdefault(name, []).append((self.open.pop(name), e))
+
+    def totals_ms(self):
+        return {k: sum(a.elapsed_time(b) for a, b in v) for k, v in self.pairs.items()}
+
+    def counts(self):
+        return {k: len(v) for k, v in self.pairs.items()}
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU arm: the oracle's C/OpenMP port (oracle/cpu_splat.c -> oracle/_cpu/libcpusplat.so)
+# ---------------------------------------------------------------------------------------------------
+def cpu_port_time(N, W, H, deg, steps, warmup, seed=0):
+    """Times fwd+bwd of one view on the host cores with the C port of the oracle.  Returns
+    (seconds_per_view, cores, M) or raises if the port is not built."""
+    from oracle import cpu_port
+    import torch
+    from oracle import torch_oracle as orc
+
+    sc = orc.synthetic_scene(N, W, H, seed=seed)
+    act = orc.activate(sc)
+    g = torch.Generator().manual_seed(1)
+    v_render = torch.randn(H, W, 3, generator=g)
+    times, M = [], 0
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        out = cpu_port.forward_backward(act, sc["viewmat"], sc["K"], W, H, deg, v_render)
+        dt = time.perf_counter() - t0
+        M = out["M"]
+        if i >= warmup:
+            times.append(dt)
+    return sum(times) / len(times), cpu_port.num_threads(), M
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    N, W, H, deg = CONFIGS[args.config]
+    # bounded sample: the SAME workload (full N, full resolution), one view per step, few steps
+    steps = max(1, min(args.steps, 3))
+    warm = 1 if args.warmup > 0 else 0
+    try:
+        sec, cores, M = cpu_port_time(N, W, H, deg, steps, warm)
+    except Exception as e:  # the port is part of the repo; failing to run it is an error worth seeing
+        print(json.dumps({"impl": "reference", "unavailable": f"oracle C port failed: {e!r}"[:200]}))
+        return 0
+    mpix = W * H / sec / 1e6
+    line = {
+        "impl": "reference", "metric": METRIC, "value": mpix, "unit": "Mpix/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": warm, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.config}: {N} gaussians SH{deg}, {W}x{H}, 1 view fwd+bwd per step, CPU"},
+        "cpu_baseline": {"value": mpix, "unit": "Mpix/s", "cores": cores, "kind": "port",
+                         "sample": f"{steps} full views (N={N}, {W}x{H}, M={M}) on {cores} host threads, oracle/cpu_splat.c"},
+        "e2e": {"value": mpix, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------------
+# B200 arm
+# ---------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the B200 arm has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    pkg = importlib.import_module("3d-gaussian-splatting_b200")
+    from oracle import torch_oracle as orc  # scene generator only (deterministic CPU generator)
+
+    N, W, H, deg = CONFIGS[args.config]
+    V = args.views_per_rank
+    sc = orc.synthetic_scene(N, W, H, seed=0)
+    act = orc.activate(sc)
+    cams = orc.circle_cameras(64)
+    leaves = {k: act[k].to(dev).clone().requires_grad_(True) for k in ("means3D", "scales", "rotations", "opacities", "shs")}
+    K = sc["K"].to(dev)
+    backend = pkg.B200Backend(K)
+    bg = torch.zeros(3, device=dev)
+    gen = torch.Generator().manual_seed(1 + rank)
+    v_render = torch.randn(H, W, 3, generator=gen).to(dev)
+    gt_host = torch.rand(H, W, 3, generator=gen).pin_memory()
+    pose_host = [cams[i].clone().pin_memory() for i in range(64)]
+    poses_dev = [cams[i].to(dev) for i in range(64)]
+    params_list = [leaves[k] for k in ("means3D", "scales", "rotations", "opacities", "shs")]
+    flat = None
+
+    def view_index(step, v):
+        return (step * world * V + rank * V + v) % 64
+
+    def step_device(step):
+        """inputs resident in HBM: pose + cotangent on device."""
+        nonlocal flat
+        for p in params_list:
+            p.grad = None
+        for v in range(V):
+            vp = {"world_view_transform": poses_dev[view_index(step, v)], "image_width": W, "image_height": H}
+            res = backend.render_with_depth(leaves, vp, bg_color=bg, render_mode="RGB", device="cuda", sh_degree=deg)
+            res["render"].backward(v_render)
+        if world > 1:
+            flat = pkg.allreduce_gradients(params_list, world * V, flat=flat)
+
+    def step_e2e(step):
+        """through the public backend call with HOST buffers: pose + ground-truth frame uploaded from pinned
+        memory every view, L1 loss, backward, loss read back (what trainer.py:270-281,485-497 does per view)."""
+        nonlocal flat
+        for p in params_list:
+            p.grad = None
+        tot = torch.zeros((), device=dev)
+        for v in range(V):
+            pose = pose_host[view_index(step, v)].to(dev, non_blocking=True)
+            gt = gt_host.to(dev, non_blocking=True)
+            vp = {"world_view_transform": pose, "image_width": W, "image_height": H}
+            res = backend.render_with_depth(leaves, vp, bg_color=bg, render_mode="RGB", device="cuda", sh_degree=deg)
+            loss = (res["render"] - gt).abs().mean()
+            loss.backward()
+            tot = tot + loss.detach()
+        if world > 1:
+            flat = pkg.allreduce_gradients(params_list, world * V, flat=flat)
+        return float(tot.item())  # D2H read of the step's result
+
+    def timed(fn, steps, warmup, timer=None):
+        for i in range(warmup):
+            fn(i)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        if timer is not None:
+            timer.enabled = True
+        l0 = pkg._lib.launch_count
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(warmup + i)
+        e1.record()
+        torch.cuda.synchronize()
+        if timer is not None:
+            timer.enabled = False
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, pkg._lib.launch_count - l0
+
+    timer = StageTimer(torch)
+    pkg._lib.stage_timer = timer
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ms_dev, launches = timed(step_device, args.steps, args.warmup, timer)
+    ms_e2e, _ = timed(step_e2e, args.steps, max(1, args.warmup // 2))
+    if rank == 0:
+        sampler.stop_flag.set()
+        sampler.join(timeout=2)
+    pkg._lib.stage_timer = None
+
+    # scene statistics for the last view (N_visible, M) and the per-stage roofline
+    with torch.no_grad():
+        cam = pkg.make_cam(poses_dev[0], K)
+        b = pkg.project_and_bin(leaves["means3D"], leaves["rotations"], leaves["scales"],
+                                leaves["opacities"].squeeze(-1).contiguous(), leaves["shs"], deg, cam, W, H)
+        M = b["M"]
+        n_vis = int((b["radii"] > 0).all(-1).sum().item())
+    views_total = args.steps * V
+    pix_per_step = world * V * W * H
+    value = pix_per_step / (ms_dev / args.steps / 1e3) / 1e6
+    e2e_val = pix_per_step / (ms_e2e / args.steps / 1e3) / 1e6
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    peaks, peak_kind = _peaks()
+    hbm = float(peaks.get("hbm_gbs", 6650.0))
+    tot = timer.totals_ms()
+    cnt = timer.counts()
+    per_view_ms = {k: tot[k] / max(cnt[k], 1) for k in tot}
+    # algorithmic bytes per launch (DESIGN.md "Kernels")
+    alg = {
+        "project_sh_fwd": n_vis * 280 + (N - n_vis) * 52,
+        "bin_emit": M * 12 + N * 16,
+        "sort_pairs": M * 24,
+        "tile_ranges": M * 8,
+        "raster_fwd": M * 44 + W * H * 20,
+        "raster_bwd": M * 44 + W * H * 24 + n_vis * 36,
+        "project_sh_bwd": n_vis * 508 + (N - n_vis) * 200,
+    }
+    stages = {}
+    for k, ms in per_view_ms.items():
+        gbs = alg.get(k, 0) / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
+        stages[k] = {"ms": round(ms, 4), "alg_MB": round(alg.get(k, 0) / 1e6, 2), "GBps": round(gbs, 1),
+                     "frac_hbm": round(gbs / hbm, 4)}
+    dom = max(per_view_ms, key=per_view_ms.get) if per_view_ms else None
+    roofline = None
+    if dom:
+        ach = stages[dom]["GBps"]
+        roofline = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": round(ach / hbm, 4),
+                    "traffic": None, "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
+                    "share_of_step": round(per_view_ms[dom] / sum(per_view_ms.values()), 3), "stages": stages}
+
+    cpu_baseline = None
+    try:
+        # bounded sample of the same workload on the host cores: one full view, C/OpenMP port of the oracle
+        sec, cores, Mc = cpu_port_time(N, W, H, deg, steps=1, warmup=0)
+        cpu_baseline = {"value": W * H / sec / 1e6, "unit": "Mpix/s", "cores": cores, "kind": "port",
+                        "sample": f"1 full view fwd+bwd (N={N}, {W}x{H}, M={Mc}), oracle/cpu_splat.c OpenMP"}
+    except Exception as e:
+        cpu_baseline = {"value": None, "unit": "Mpix/s", "cores": 0, "kind": "port", "sample": f"failed: {e!r}"[:160]}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": "Mpix/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.config}: {N} gaussians SH{deg}, {W}x{H}, {V} view(s)/rank/step fwd+bwd"
+                               + (", 1 NCCL all-reduce of 59N-float flat gradient/step" if world > 1 else ""),
+                   "N": N, "N_visible": n_vis, "M_isects": M, "views_per_rank": V,
+                   "l2": "inputs larger than L2 (params 236 MB + keys/records > 126 MB); no explicit flush"},
+        "e2e": {"value": e2e_val, "unit": "Mpix/s", "h2d_bytes_per_step": V * (W * H * 3 * 4 + 64), "d2h_bytes_per_step": 4,
+                "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": launches,
+        "clocks": sampler.summary(),
+        "roofline": roofline,
+        "cpu_baseline": cpu_baseline,
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="A", choices=sorted(CONFIGS))
+    ap.add_argument("--views-per-rank", type=int, default=4)
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "b200":
+        args.warmup = 3
+    sys.exit(run_reference(args) if args.impl == "reference" else run_b200(args))
+
+
+if __name__ == "__main__":
+    main()

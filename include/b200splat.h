@@ -1,0 +1,132 @@
+/*
+ * b200splat.h — C ABI of the B200-native (sm_100a) Gaussian-splatting rasterizer.
+ *
+ * This is the drop-in boundary for ONE hot path of ShayManor/3d-gaussian-splatting: the call
+ *     gsplat.rasterization(means, quats, scales, opacities, colors=shs, viewmats[1,4,4], Ks[1,3,3],
+ *                          width, height, packed=False, render_mode, sh_degree, backgrounds[1,3])
+ * issued at reference  src/backends/gsplat_backend.py:83-97 and :168-182, its autograd backward
+ * (triggered at src/training/trainer.py:505-511), and the densification statistic of
+ * src/training/trainer.py:786-791.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in `_host`;
+ *   - no allocation, no exceptions, no torch types; caller owns every buffer;
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*); only functions whose
+ *     documentation says "synchronises" block the host;
+ *   - return 0 on success, B200_EARG (-1) bad argument, B200_ESCRATCH (-2) scratch too small,
+ *     B200_ECUDA (-3) CUDA error (text in b200_last_error()).
+ *   - quaternions (w,x,y,z); viewmat row-major world->camera, OpenCV axes; images row-major HWC;
+ *     tile = 16x16 px; tile_id = ty*tile_w + tx; one camera per call (reference passes batch dim 1,
+ *     gsplat_backend.py:174-175).
+ *
+ * Splat record ("splats", [N,12] fp32, 48 B, 16-B aligned) written by the projection stage and
+ * gathered by the blend stages:
+ *     [0] mean2d.x  [1] mean2d.y  [2] conic.A  [3] conic.B
+ *     [4] conic.C   [5] opacity   [6] red      [7] green
+ *     [8] blue      [9] depth     [10] 0       [11] 0
+ * The gradient record ("v_splats", same shape) holds the cotangent of each slot.
+ */
+#ifndef B200SPLAT_H
+#define B200SPLAT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK 0
+#define B200_EARG (-1)
+#define B200_ESCRATCH (-2)
+#define B200_ECUDA (-3)
+
+#define B200_TILE 16
+#define B200_SPLAT_FLOATS 12
+
+/* channel sets of the blend stages (reference render_mode parsing, gsplat_backend.py:190-201) */
+#define B200_CH_RGB 0   /* "RGB"            -> 3 channels           */
+#define B200_CH_D 1     /* "D" / "ED"       -> 1 channel (depth)    */
+#define B200_CH_RGBD 2  /* "RGB+D"/"RGB+ED" -> 4 channels (rgb, d)  */
+
+/* Camera block passed by value from the host: 16 viewmat floats (row-major 4x4 world->camera),
+ * then fx, fy, cx, cy (pixels; K[0,0],K[1,1],K[0,2],K[1,2] of gsplat_backend.py:10,175),
+ * then near_plane, far_plane, eps2d, radius_clip (gsplat defaults 0.01, 1e10, 0.3, 0.0). */
+#define B200_CAM_FLOATS 24
+
+int b200_version(void);
+const char* b200_last_error(void);
+
+/* ---- stage 1: EWA projection + SH colour + per-Gaussian tile count (fused) -------------------
+ * Replaces gsplat fully_fused_projection + spherical_harmonics + clamp_min(c+0.5,0) + the counting
+ * half of isect_tiles, as invoked through gsplat_backend.py:168-182.
+ *   means[N,3] quats[N,4] scales[N,3] (post-exp) opacities[N] (post-sigmoid) shs[N,sh_coeffs,3]
+ *   sh_degree in 0..3 with (sh_degree+1)^2 <= sh_coeffs; sh_degree < 0 => `shs` is [N,3] plain colours.
+ * Outputs: radii[N,2] int32, splats[N,12], tiles_per_gauss[N] int32,
+ *          block_sums[b200_project_blocks(N)] int64 (sum of tiles_per_gauss per 256-Gaussian block). */
+int64_t b200_project_blocks(int64_t N);
+int b200_project_sh_fwd(const float* means, const float* quats, const float* scales,
+                        const float* opacities, const float* shs, int sh_coeffs, int sh_degree,
+                        int64_t N, const float* cam_host, int width, int height,
+                        int32_t* radii, float* splats, int32_t* tiles_per_gauss,
+                        int64_t* block_sums, void* stream);
+
+/* ---- stage 2a: exclusive scan of block sums; writes block_offsets[nblocks] and total[1] -------
+ * (the cumsum half of gsplat isect_tiles).  Single CTA; nblocks = b200_project_blocks(N). */
+int b200_bin_scan(const int64_t* block_sums, int64_t nblocks, int64_t* block_offsets,
+                  int64_t* total, void* stream);
+
+/* ---- stage 2b: key emission ---------------------------------------------------------------
+ * isect_ids[M] int64 = (tile_id << 32) | depth_bits, flatten_ids[M] int32 = Gaussian index, in
+ * gsplat's emission order (Gaussian-major, then tile row-major).  cum_tiles (optional, may be NULL)
+ * receives the inclusive int64 cumsum [N].  M is the value b200_bin_scan wrote to total[0]. */
+int b200_bin_emit(const float* splats, const int32_t* radii, const int32_t* tiles_per_gauss,
+                  const int64_t* block_offsets, int64_t N, int width, int height, int64_t M,
+                  int64_t* isect_ids, int32_t* flatten_ids, int64_t* cum_tiles, void* stream);
+
+/* ---- stage 2c: stable LSD radix sort of (uint64 key, uint32 value) pairs over key bits
+ * [0, end_bit) (replaces cub::DeviceRadixSort::SortPairs inside gsplat isect_tiles(sort=True)).
+ * keys_a/vals_a hold the input; *result_in_b tells which buffer pair holds the sorted output.
+ * Scratch: b200_sort_scratch_bytes(M). */
+size_t b200_sort_scratch_bytes(int64_t M);
+int b200_sort_pairs(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b,
+                    int64_t M, int end_bit, void* scratch, size_t scratch_bytes,
+                    int* result_in_b_host, void* stream);
+
+/* ---- stage 2d: per-tile ranges (gsplat isect_offset_encode) ---------------------------------
+ * offsets[n_tiles] int32 = first sorted index whose tile id >= t; all M's for trailing empty tiles. */
+int b200_tile_ranges(const int64_t* sorted_isect_ids, int64_t M, int n_tiles, int32_t* offsets,
+                     void* stream);
+
+/* ---- stage 3: forward blend (gsplat rasterize_to_pixels forward) ----------------------------
+ * render[H,W,CH] alpha[H,W] last_ids[H,W] (index into the sorted list of the last composited
+ * Gaussian, -1 if none).  background_host: CH floats or NULL (zeros). */
+int b200_raster_fwd(const float* splats, const int32_t* flatten_ids, const int32_t* offsets,
+                    int64_t M, int width, int height, int channels, const float* background_host,
+                    float* render, float* alpha, int32_t* last_ids, void* stream);
+
+/* ---- stage 4a: backward blend (gsplat rasterize_to_pixels backward) -------------------------
+ * v_render[H,W,CH], v_alpha[H,W] or NULL.  ACCUMULATES into v_splats[N,12] (caller zeroes). */
+int b200_raster_bwd(const float* splats, const int32_t* flatten_ids, const int32_t* offsets,
+                    int64_t M, int width, int height, int channels, const float* background_host,
+                    const float* alpha, const int32_t* last_ids, const float* v_render,
+                    const float* v_alpha, float* v_splats, void* stream);
+
+/* ---- stage 4b: projection + SH backward ----------------------------------------------------
+ * Chains v_splats through conic/mean2d/depth/colour to the five input tensors.  Writes (does not
+ * accumulate) v_means[N,3] v_quats[N,4] v_scales[N,3] v_opacities[N] v_shs[N,sh_coeffs,3]. */
+int b200_project_sh_bwd(const float* means, const float* quats, const float* scales,
+                        const float* opacities, const float* shs, int sh_coeffs, int sh_degree,
+                        int64_t N, const float* cam_host, int width, int height,
+                        const int32_t* radii, const float* v_splats,
+                        float* v_means, float* v_quats, float* v_scales, float* v_opacities,
+                        float* v_shs, void* stream);
+
+/* ---- stage 5: densification statistics (reference trainer.py:786-791) -------------------------
+ * accum[N,3] += ||xyz_grad[n,:]||_2 (broadcast over the 3 columns); count[N] += 1. */
+int b200_densify_stats(const float* xyz_grad, int64_t N, float* accum, float* count, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SPLAT_H */

@@ -1,0 +1,354 @@
+"""GPU parity tests: every CUDA stage, called through the C ABI, against the CPU oracle
+(oracle/torch_oracle.py — a restatement of gsplat 1.5.x as the reference calls it; parity unpinned,
+see its header) on identical seeded inputs.
+
+Tolerances (BASELINE.json north_star): tile keys / sort order / per-tile ranges bit-exact; rendered RGB
+max-abs <= 1e-4; parameter gradients relative error <= 1e-3.
+"""
+import ctypes as C
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+
+
+def _scene(oracle, N, W, H, seed=0):
+    sc = oracle.synthetic_scene(N, W, H, seed=seed)
+    act = oracle.activate(sc)
+    return sc, act
+
+
+def _cuda(d):
+    return {k: (v.to(DEV) if isinstance(v, torch.Tensor) else v) for k, v in d.items()}
+
+
+def _oracle_full(oracle, act, sc, W, H, deg, mode="RGB", bg=None, margin=0.0, dtype=torch.float32):
+    return oracle.rasterization(
+        act["means3D"].to(dtype), act["rotations"].to(dtype), act["scales"].to(dtype),
+        act["opacities"].squeeze(-1).to(dtype), act["shs"].to(dtype), sc["viewmat"], sc["K"], W, H,
+        sh_degree=deg, background=bg, render_mode=mode, margin_eps=margin)
+
+
+def _gpu_full(pkg, act, sc, W, H, deg, mode="RGB", bg=None, requires_grad=False):
+    a = _cuda(act)
+    leaves = {}
+    for k in ("means3D", "rotations", "scales", "opacities", "shs"):
+        t = a[k].clone()
+        if k == "opacities":
+            t = t.squeeze(-1)
+        t.requires_grad_(requires_grad)
+        leaves[k] = t
+    r, al, meta = pkg.rasterization(
+        leaves["means3D"], leaves["rotations"], leaves["scales"], leaves["opacities"], leaves["shs"],
+        sc["viewmat"].to(DEV)[None], sc["K"].to(DEV)[None], W, H, sh_degree=deg, render_mode=mode,
+        backgrounds=None if bg is None else bg.to(DEV)[None])
+    return r[0], al[0], meta, leaves
+
+
+# ------------------------------------------------------------------------------------------------
+# stage 1: projection + SH
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("deg", [0, 1, 2, 3])
+def test_projection_and_sh_match_oracle(pkg, oracle, deg):
+    N, W, H = 20000, 320, 192
+    sc, act = _scene(oracle, N, W, H)
+    proj = oracle.project(act["means3D"], act["rotations"], act["scales"], act["opacities"].squeeze(-1),
+                          sc["viewmat"], sc["K"], W, H)
+    vis_o = (proj["radii"] > 0).all(-1)
+    col_o = oracle.sh_colors(act["means3D"], act["shs"], sc["viewmat"], deg, vis_o)
+    _, _, meta, _ = _gpu_full(pkg, act, sc, W, H, deg)
+    radii_g = meta["radii"][0].cpu()
+    vis_g = (radii_g > 0).all(-1)
+    # culling / integer radii: identical up to fp32 rounding at a ceil() or cull boundary
+    mism = (radii_g != proj["radii"]).any(-1)
+    assert mism.float().mean().item() <= 2e-3, f"radii mismatch fraction {mism.float().mean().item()}"
+    both = vis_o & vis_g & ~mism
+    assert both.sum() > 0.5 * N
+    for name, ref in (("means2d", proj["means2d"]), ("conics", proj["conics"]), ("depths", proj["depths"]),
+                      ("colors", col_o)):
+        got = meta[name][0].cpu()
+        torch.testing.assert_close(got[both], ref[both], rtol=2e-4, atol=2e-5, msg=lambda m: f"{name}: {m}")
+    # culled Gaussians carry zeros and zero tile counts
+    assert (meta["tiles_per_gauss"][0].cpu()[~vis_g] == 0).all()
+
+
+def test_culling_cases(pkg, oracle):
+    """behind the near plane, opacity < 1/255, far outside the frustum -> radii 0."""
+    W, H = 64, 64
+    K = torch.tensor([[50.0, 0, 32], [0, 50.0, 32], [0, 0, 1]])
+    means = torch.tensor([[0, 0, 5.0], [0, 0, -1.0], [0, 0, 5.0], [100.0, 0, 5.0], [0, 0, 0.005]])
+    quats = torch.tensor([[1.0, 0, 0, 0]]).repeat(5, 1)
+    scales = torch.full((5, 3), 0.1)
+    opac = torch.tensor([0.9, 0.9, 0.003, 0.9, 0.9])
+    shs = torch.zeros(5, 16, 3)
+    r, a, meta = pkg.rasterization(means.to(DEV), quats.to(DEV), scales.to(DEV), opac.to(DEV), shs.to(DEV),
+                                   torch.eye(4, device=DEV)[None], K.to(DEV)[None], W, H, sh_degree=3)
+    radii = meta["radii"][0].cpu()
+    assert (radii[0] > 0).all()
+    assert (radii[1:] == 0).all()
+    proj = oracle.project(means, quats, scales, opac, torch.eye(4), K, W, H)
+    assert torch.equal(radii, proj["radii"])
+
+
+# ------------------------------------------------------------------------------------------------
+# stage 2: binning / sort / ranges — bit exact
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("N,W,H", [(3000, 160, 96), (50000, 640, 360), (20000, 1920, 1080)])
+def test_binning_sort_ranges_bit_exact(pkg, oracle, N, W, H):
+    sc, act = _scene(oracle, N, W, H, seed=3)
+    a = _cuda(act)
+    cam = pkg.make_cam(sc["viewmat"], sc["K"])
+    b = pkg.project_and_bin(a["means3D"], a["rotations"], a["scales"], a["opacities"].squeeze(-1).contiguous(),
+                            a["shs"], 3, cam, W, H, keep_unsorted=True)
+    sp = b["splats"].cpu()
+    radii = b["radii"].cpu()
+    # binning oracle on the GPU's own projection outputs ("bit-exact given identical inputs")
+    ob = oracle.bin_tiles(sp[:, 0:2], radii, sp[:, 9], W, H)
+    assert torch.equal(b["tiles_per_gauss"].cpu(), ob["tiles_per_gauss"])
+    assert b["M"] == int(ob["cum_tiles"][-1])
+    assert torch.equal(b["isect_ids_unsorted"].cpu(), ob["isect_ids"])
+    assert torch.equal(b["flatten_ids_unsorted"].cpu(), ob["flatten_ids"])
+    ids_s, flat_s, offs = oracle.sort_and_ranges(ob["isect_ids"], ob["flatten_ids"], ob["tile_w"], ob["tile_h"])
+    assert torch.equal(b["isect_ids"].cpu(), ids_s)
+    assert torch.equal(b["flatten_ids"].cpu(), flat_s)
+    assert torch.equal(b["isect_offsets"].cpu(), offs)
+
+
+def test_cum_tiles_output(pkg, oracle):
+    N, W, H = 5000, 320, 192
+    sc, act = _scene(oracle, N, W, H, seed=5)
+    a = _cuda(act)
+    lib, L = pkg._lib.lib, pkg._lib
+    cam = pkg.make_cam(sc["viewmat"], sc["K"])
+    b = pkg.project_and_bin(a["means3D"], a["rotations"], a["scales"], a["opacities"].squeeze(-1).contiguous(),
+                            a["shs"], 3, cam, W, H)
+    nb = lib.b200_project_blocks(N)
+    tpg = b["tiles_per_gauss"]
+    bs = tpg.to(torch.int64).reshape(-1)
+    pad = nb * 256 - N
+    bs = torch.cat([bs, bs.new_zeros(pad)]).view(nb, 256).sum(1).contiguous()
+    bo = torch.empty(nb, dtype=torch.int64, device=DEV)
+    tot = torch.zeros(1, dtype=torch.int64, device=DEV)
+    L.check(lib.b200_bin_scan(bs.data_ptr(), nb, bo.data_ptr(), tot.data_ptr(), None), "scan")
+    M = int(tot.item())
+    ids = torch.empty(M, dtype=torch.int64, device=DEV)
+    fl = torch.empty(M, dtype=torch.int32, device=DEV)
+    cum = torch.empty(N, dtype=torch.int64, device=DEV)
+    L.check(lib.b200_bin_emit(b["splats"].data_ptr(), b["radii"].data_ptr(), tpg.data_ptr(), bo.data_ptr(), N, W, H, M,
+                              ids.data_ptr(), fl.data_ptr(), cum.data_ptr(), None), "emit")
+    torch.cuda.synchronize()
+    assert torch.equal(cum.cpu(), torch.cumsum(tpg.cpu().to(torch.int64), 0))
+
+
+@pytest.mark.parametrize("n", [0, 1, 31, 4095, 4096, 4097, 100_003, 3_000_000])
+@pytest.mark.parametrize("end_bit", [45, 47, 64, 9])
+def test_radix_sort_pairs_stable(pkg, n, end_bit):
+    lib, L = pkg._lib.lib, pkg._lib
+    g = torch.Generator().manual_seed(n + end_bit)
+    hi = min(end_bit, 62)
+    keys = torch.randint(0, 2 ** hi, (max(n, 1),), generator=g, dtype=torch.int64)[:n]
+    if n > 10:  # many duplicate keys -> exercises stability
+        keys[: n // 2] = keys[: n // 2] & 0xFFF
+    if end_bit == 64 and n > 0:
+        keys[::7] |= (1 << 62)
+    vals = torch.arange(n, dtype=torch.int32)
+    ka, va = keys.to(DEV), vals.to(DEV)
+    if n == 0:
+        ka = torch.empty(1, dtype=torch.int64, device=DEV)
+        va = torch.empty(1, dtype=torch.int32, device=DEV)
+    kb, vb = torch.empty_like(ka), torch.empty_like(va)
+    sb = lib.b200_sort_scratch_bytes(n)
+    scratch = torch.empty(sb, dtype=torch.uint8, device=DEV)
+    in_b = C.c_int(0)
+    L.check(lib.b200_sort_pairs(ka.data_ptr(), va.data_ptr(), kb.data_ptr(), vb.data_ptr(), n, end_bit,
+                                scratch.data_ptr(), sb, C.byref(in_b), None), "sort")
+    torch.cuda.synchronize()
+    ks, vs = (kb, vb) if in_b.value else (ka, va)
+    order = torch.sort(keys, stable=True).indices
+    assert torch.equal(ks[:n].cpu(), keys[order])
+    assert torch.equal(vs[:n].cpu(), vals[order])
+
+
+def test_sort_scratch_too_small_is_an_error(pkg):
+    lib = pkg._lib.lib
+    t = torch.zeros(5000, dtype=torch.int64, device=DEV)
+    v = torch.zeros(5000, dtype=torch.int32, device=DEV)
+    s = torch.zeros(16, dtype=torch.uint8, device=DEV)
+    rc = lib.b200_sort_pairs(t.data_ptr(), v.data_ptr(), t.data_ptr(), v.data_ptr(), 5000, 45, s.data_ptr(), 16, None, None)
+    assert rc == -2 and b"scratch" in lib.b200_last_error()
+
+
+# ------------------------------------------------------------------------------------------------
+# stage 3: forward blend
+# ------------------------------------------------------------------------------------------------
+def _assert_image_close(got, ref, marginal, tol=1e-4):
+    err = (got - ref).abs().amax(-1)
+    ok = ~marginal if marginal is not None else torch.ones_like(err, dtype=torch.bool)
+    assert err[ok].max().item() <= tol, f"max abs err {err[ok].max().item()} on non-marginal pixels"
+    if marginal is not None:
+        # a pixel whose skip/stop decision sits within fp32 rounding of its threshold may differ by one term
+        assert marginal.float().mean().item() < 0.02
+        assert err.max().item() < 0.05
+
+
+@pytest.mark.parametrize("N,W,H,deg", [(4000, 160, 96, 3), (30000, 320, 200, 3), (4000, 150, 90, 1)])
+def test_forward_render_matches_oracle(pkg, oracle, N, W, H, deg):
+    sc, act = _scene(oracle, N, W, H, seed=1)
+    bg = torch.tensor([0.2, 0.5, 0.7])
+    r_o, a_o, m_o = _oracle_full(oracle, act, sc, W, H, deg, bg=bg, margin=1e-3)
+    r_g, a_g, meta, _ = _gpu_full(pkg, act, sc, W, H, deg, bg=bg)
+    assert r_g.shape == (H, W, 3) and a_g.shape == (H, W, 1)
+    _assert_image_close(r_g.cpu(), r_o, m_o["marginal"])
+    _assert_image_close(a_g.cpu(), a_o, m_o["marginal"])
+
+
+def test_forward_blend_given_identical_inputs(pkg, oracle):
+    """Blend stage alone: oracle.rasterize on the GPU's own splats / sorted ids / ranges."""
+    N, W, H = 20000, 320, 200
+    sc, act = _scene(oracle, N, W, H, seed=2)
+    r_g, a_g, meta, _ = _gpu_full(pkg, act, sc, W, H, 3)
+    r_o, a_o, last_o, marg = oracle.rasterize(
+        meta["means2d"][0].cpu(), meta["conics"][0].cpu(), meta["colors"][0].cpu(), act["opacities"].squeeze(-1),
+        W, H, meta["isect_offsets"][0].cpu(), meta["flatten_ids"].cpu(), None, margin_eps=1e-3)
+    _assert_image_close(r_g.cpu(), r_o, marg)
+    last_g = meta["last_ids"][0].cpu()
+    comp = (a_o[..., 0] > 0) & ~marg
+    assert torch.equal(last_g[comp], last_o[comp])
+    assert (last_g[(a_o[..., 0] == 0) & ~marg] == -1).all()
+
+
+@pytest.mark.parametrize("mode", ["D", "ED", "RGB+D", "RGB+ED"])
+def test_depth_render_modes(pkg, oracle, mode):
+    N, W, H = 5000, 160, 96
+    sc, act = _scene(oracle, N, W, H, seed=4)
+    bg = torch.tensor([0.1, 0.2, 0.3])
+    r_o, a_o, m_o = _oracle_full(oracle, act, sc, W, H, 3, mode=mode, bg=bg, margin=1e-3)
+    r_g, a_g, _, _ = _gpu_full(pkg, act, sc, W, H, 3, mode=mode, bg=bg)
+    assert r_g.shape == r_o.shape
+    ok = ~m_o["marginal"]
+    # depth channels are O(10): relative tolerance
+    err = ((r_g.cpu() - r_o).abs() / (1.0 + r_o.abs())).amax(-1)
+    assert err[ok].max().item() <= 2e-4
+
+
+def test_empty_and_degenerate_inputs(pkg):
+    W, H = 40, 24
+    K = torch.tensor([[30.0, 0, 20], [0, 30.0, 12], [0, 0, 1]], device=DEV)
+    vm = torch.eye(4, device=DEV)
+    # all Gaussians culled -> background only, M = 0
+    means = torch.tensor([[0.0, 0, -5.0]] * 7, device=DEV)
+    r, a, meta = pkg.rasterization(means, torch.tensor([[1.0, 0, 0, 0]] * 7, device=DEV), torch.full((7, 3), 0.1, device=DEV),
+                                   torch.full((7,), 0.5, device=DEV), torch.zeros(7, 16, 3, device=DEV), vm[None], K[None],
+                                   W, H, sh_degree=3, backgrounds=torch.tensor([[0.25, 0.5, 0.75]], device=DEV))
+    assert meta["flatten_ids"].numel() == 0
+    assert torch.allclose(r[0], torch.tensor([0.25, 0.5, 0.75], device=DEV).expand(H, W, 3))
+    assert (a == 0).all() and (meta["isect_offsets"] == 0).all()
+
+
+# ------------------------------------------------------------------------------------------------
+# stage 4: backward
+# ------------------------------------------------------------------------------------------------
+def _rel(got, ref):
+    return ((got - ref).norm() / ref.norm().clamp_min(1e-12)).item()
+
+
+@pytest.mark.parametrize("N,W,H,deg,mode", [(3000, 128, 80, 3, "RGB"), (3000, 128, 80, 2, "RGB"),
+                                            (12000, 240, 136, 3, "RGB"), (3000, 128, 80, 3, "RGB+ED"),
+                                            (3000, 128, 80, 0, "RGB+D")])
+def test_gradients_match_oracle_autograd(pkg, oracle, N, W, H, deg, mode):
+    sc, act = _scene(oracle, N, W, H, seed=7)
+    bg = torch.tensor([0.3, 0.1, 0.6])
+    nch = 3 if mode == "RGB" else 4
+    gen = torch.Generator().manual_seed(1)
+    v_render = torch.randn(H, W, nch, generator=gen)
+    v_alpha = torch.randn(H, W, 1, generator=gen) if mode != "RGB" else None
+    if nch == 4:
+        v_render[..., 3] *= 0.05
+
+    # oracle in fp64 autograd: the gradient "truth" (fp32 rounding of the oracle itself would otherwise dominate)
+    leaves_o = {k: act[k].double().clone().requires_grad_(True) for k in ("means3D", "rotations", "scales", "opacities", "shs")}
+    r_o, a_o, m_o = oracle.rasterization(leaves_o["means3D"], leaves_o["rotations"], leaves_o["scales"],
+                                         leaves_o["opacities"].squeeze(-1), leaves_o["shs"], sc["viewmat"].double(),
+                                         sc["K"].double(), W, H, sh_degree=deg, background=bg.double(), render_mode=mode)
+    loss_o = (r_o * v_render.double()).sum()
+    if v_alpha is not None:
+        loss_o = loss_o + (a_o * v_alpha.double()).sum()
+    loss_o.backward()
+
+    r_g, a_g, meta, leaves_g = _gpu_full(pkg, act, sc, W, H, deg, mode=mode, bg=bg, requires_grad=True)
+    loss_g = (r_g * v_render.to(DEV)).sum()
+    if v_alpha is not None:
+        loss_g = loss_g + (a_g * v_alpha.to(DEV)).sum()
+    loss_g.backward()
+
+    # the comparison is only meaningful if both made the same discrete decisions (same binning)
+    same = torch.equal(meta["radii"][0].cpu(), m_o["radii"])
+    for k in ("means3D", "rotations", "scales", "opacities", "shs"):
+        go = leaves_o[k].grad.float().reshape(leaves_g[k].shape)
+        gg = leaves_g[k].grad.cpu()
+        assert torch.isfinite(gg).all()
+        rel = _rel(gg, go)
+        assert rel <= (1e-3 if same else 2e-2), f"{k}: relative gradient error {rel} (same radii: {same})"
+    # SH coefficients above the active degree get exactly zero gradient (trainer.py:77-87 schedule)
+    nb = (deg + 1) ** 2
+    assert (leaves_g["shs"].grad[:, nb:, :] == 0).all()
+
+
+def test_backward_without_v_alpha_and_no_grad_mode(pkg, oracle):
+    N, W, H = 2000, 96, 64
+    sc, act = _scene(oracle, N, W, H, seed=9)
+    r_g, a_g, meta, leaves = _gpu_full(pkg, act, sc, W, H, 3, requires_grad=True)
+    r_g.square().mean().backward()  # alpha unused, like the trainer's loss (trainer.py:480-493)
+    assert all(torch.isfinite(t.grad).all() for t in leaves.values())
+    with torch.no_grad():
+        r2, _, _, _ = _gpu_full(pkg, act, sc, W, H, 3, requires_grad=True)
+    assert not r2.requires_grad
+    assert torch.equal(r2, r_g.detach())  # forward is deterministic
+
+
+# ------------------------------------------------------------------------------------------------
+# stage 5 + boundary
+# ------------------------------------------------------------------------------------------------
+def test_densify_stats(pkg, oracle):
+    N = 100_001
+    g = torch.Generator().manual_seed(0)
+    grad = torch.randn(N, 3, generator=g)
+    accum = torch.rand(N, 3, generator=g)
+    count = torch.randint(0, 5, (N, 1), generator=g).float()
+    a_g, c_g = accum.to(DEV), count.to(DEV)
+    pkg.densify_stats(a_g, c_g, grad.to(DEV))
+    oracle.densify_stats(accum, count, grad)
+    torch.testing.assert_close(a_g.cpu(), accum, rtol=1e-6, atol=1e-7)
+    assert torch.equal(c_g.cpu(), count)
+
+
+def test_backend_result_dict_matches_reference_contract(pkg, oracle):
+    """Keys/shapes of gsplat_backend.py:185-208 for every render_mode; trainer-style call."""
+    N, W, H = 3000, 112, 64
+    sc, act = _scene(oracle, N, W, H, seed=11)
+    be = pkg.B200Backend(sc["K"].to(DEV))
+    params = _cuda(act)
+    vp = {"world_view_transform": sc["viewmat"].to(DEV), "projection_matrix": torch.eye(4, device=DEV),
+          "image_width": W, "image_height": H}
+    res = be.render_with_depth(params, vp, bg_color=torch.zeros(3, device=DEV), render_mode="RGB", device="cuda", sh_degree=2)
+    assert set(res) == {"alpha", "render", "means2d", "radii", "visibility_filter"}
+    assert res["render"].shape == (H, W, 3) and res["alpha"].shape == (H, W, 1)
+    assert res["means2d"].shape == (N, 2) and res["radii"].shape == (N, 2) and res["radii"].dtype == torch.int32
+    assert res["visibility_filter"].dtype == torch.bool
+    res = be.render_with_depth(params, vp)  # eval-style: defaults RGB+ED, sh_degree -> 3 (eval.py:180-183)
+    assert set(res) == {"alpha", "render", "expected_depth", "means2d", "radii", "visibility_filter"}
+    assert res["expected_depth"].shape == (H, W)
+    for mode, key in (("D", "accumulated_depth"), ("ED", "expected_depth"), ("RGB+D", "accumulated_depth")):
+        res = be.render_with_depth(params, vp, render_mode=mode)
+        assert res[key].shape == (H, W)
+    single = be.render_single(params, vp, torch.zeros(3, device=DEV))
+    assert single["render"].shape == (H, W, 3) and single["depth"].shape == (H, W)
+    batch = be.render_batch(params, vp["world_view_transform"][None].repeat(2, 1, 1), torch.eye(4, device=DEV)[None].repeat(2, 1, 1),
+                            W, H, torch.zeros(3, device=DEV), "cuda")
+    assert batch["images"].shape == (2, 3, H, W) and batch["alphas"].shape == (2, 1, H, W)
+    with pytest.raises(RuntimeError):
+        be.render_with_depth(params, vp, device="cpu")
