@@ -1,0 +1,200 @@
+"""CPU tests of the checker itself (the reference pins nothing on this path — SURVEY.md §4/§8c — so the
+oracle is validated against closed forms, finite differences and invariances, and the C/OpenMP port
+against the PyTorch oracle and the committed golden fixture)."""
+import math
+import os
+
+import pytest
+import torch
+
+from oracle import cpu_port
+from oracle import torch_oracle as orc
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "splat_small.pt")
+
+
+def _scene(N, W, H, seed=0, dtype=torch.float32):
+    sc = orc.synthetic_scene(N, W, H, seed=seed, dtype=dtype)
+    return sc, orc.activate(sc)
+
+
+def _full(act, sc, W, H, deg, **kw):
+    return orc.rasterization(act["means3D"], act["rotations"], act["scales"], act["opacities"].squeeze(-1), act["shs"],
+                             sc["viewmat"].to(act["means3D"].dtype), sc["K"].to(act["means3D"].dtype), W, H,
+                             sh_degree=deg, **kw)
+
+
+# ---- closed forms ---------------------------------------------------------------------------------
+def test_single_isotropic_gaussian_at_image_centre():
+    W = H = 32
+    f = 40.0
+    K = torch.tensor([[f, 0, 16.0], [0, f, 16.0], [0, 0, 1]])
+    z, s, o = 4.0, 0.2, 0.8
+    means = torch.tensor([[0.0, 0.0, z]])
+    shs = torch.zeros(1, 16, 3)
+    shs[0, 0] = torch.tensor([0.3, -0.2, 0.1]) / orc.SH_C0
+    r, a, m = orc.rasterization(means, torch.tensor([[1.0, 0, 0, 0]]), torch.full((1, 3), s), torch.tensor([o]), shs,
+                                torch.eye(4), K, W, H, sh_degree=0, background=torch.zeros(3))
+    var = (f * s / z) ** 2 + 0.3  # J Sigma J^T + eps2d
+    assert torch.allclose(m["means2d"][0], torch.tensor([16.0, 16.0]))
+    assert torch.allclose(m["conics"][0], torch.tensor([1 / var, 0.0, 1 / var]), rtol=1e-5)
+    ext = min(3.33, math.sqrt(2 * math.log(o * 255)))
+    assert m["radii"][0].tolist() == [math.ceil(ext * math.sqrt(var))] * 2
+    # pixel (15,15) centre is at (15.5,15.5): d^2 = 0.5
+    al = o * math.exp(-0.5 * 0.5 / var)
+    assert abs(a[15, 15, 0].item() - al) < 1e-6
+    assert torch.allclose(r[15, 15], al * torch.tensor([0.8, 0.3, 0.6]), atol=1e-6)
+
+
+def test_depth_order_and_early_termination():
+    W = H = 16
+    K = torch.tensor([[20.0, 0, 8.0], [0, 20.0, 8.0], [0, 0, 1]])
+    means = torch.tensor([[0, 0, 6.0], [0, 0, 3.0], [0, 0, 9.0]])  # emitted far, near, farthest
+    shs = torch.zeros(3, 16, 3)
+    shs[:, 0, 0] = torch.tensor([1.0, 0.0, -1.0])
+    r, a, m = orc.rasterization(means, torch.tensor([[1.0, 0, 0, 0]] * 3), torch.full((3, 3), 0.5), torch.tensor([0.9] * 3),
+                                shs, torch.eye(4), K, W, H, sh_degree=0)
+    t0 = m["isect_offsets"][0, 0].item()
+    assert m["flatten_ids"][t0:t0 + 3].tolist() == [1, 0, 2]  # sorted by depth inside the tile
+    assert (m["isect_ids"][1:] >= m["isect_ids"][:-1]).all()
+
+
+def test_culls():
+    W = H = 64
+    K = torch.tensor([[50.0, 0, 32], [0, 50.0, 32], [0, 0, 1]])
+    means = torch.tensor([[0, 0, 5.0], [0, 0, -1.0], [0, 0, 5.0], [100.0, 0, 5.0], [0, 0, 0.005]])
+    p = orc.project(means, torch.tensor([[1.0, 0, 0, 0]]).repeat(5, 1), torch.full((5, 3), 0.1),
+                    torch.tensor([0.9, 0.9, 0.003, 0.9, 0.9]), torch.eye(4), K, W, H)
+    assert (p["radii"][0] > 0).all() and (p["radii"][1:] == 0).all()
+
+
+# ---- invariances ----------------------------------------------------------------------------------
+def test_image_invariant_under_gaussian_permutation_and_rigid_motion():
+    N, W, H = 800, 64, 48
+    sc, act = _scene(N, W, H, seed=2)
+    r0, a0, _ = _full(act, sc, W, H, 3)
+    perm = torch.randperm(N, generator=torch.Generator().manual_seed(0))
+    actp = {k: v[perm] for k, v in act.items()}
+    r1, _, _ = _full(actp, sc, W, H, 3)
+    assert (r0 - r1).abs().max() < 1e-5  # depth ties are measure-zero in this scene
+    assert (a0 <= 1.0).all() and (a0 >= 0).all()
+    # rigid motion of scene and camera together (rotation about z + translation) leaves the image unchanged
+    th = 0.3
+    Rw = torch.tensor([[math.cos(th), -math.sin(th), 0], [math.sin(th), math.cos(th), 0], [0, 0, 1.0]])
+    tw = torch.tensor([0.3, -0.2, 0.5])
+    act2 = dict(act)
+    act2["means3D"] = act["means3D"] @ Rw.T + tw
+    qw = torch.tensor([math.cos(th / 2), 0, 0, math.sin(th / 2)])
+    q = act["rotations"]
+    w1, x1, y1, z1 = qw
+    w2, x2, y2, z2 = q.unbind(-1)
+    act2["rotations"] = torch.stack([w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2, w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2,
+                                     w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2, w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2], -1)
+    sc2 = dict(sc)
+    vm = torch.eye(4)
+    vm[:3, :3] = Rw.T
+    vm[:3, 3] = -(Rw.T @ tw)
+    sc2["viewmat"] = vm
+    r2, _, _ = _full(act2, sc2, W, H, 0)  # degree 0: view direction changes in world frame for higher degrees
+    r0d, _, _ = _full(act, sc, W, H, 0)
+    assert (r0d - r2).abs().max() < 2e-4
+
+
+# ---- finite differences (fp64) ---------------------------------------------------------------------
+@pytest.mark.parametrize("mode", ["RGB", "RGB+ED"])
+def test_oracle_autograd_matches_finite_differences(mode):
+    N, W, H = 24, 32, 32
+    sc, act = _scene(N, W, H, seed=4, dtype=torch.float64)
+    act["scales"] = act["scales"] * 6  # make them cover a few pixels
+    nch = 3 if mode == "RGB" else 4
+    v = torch.randn(H, W, nch, dtype=torch.float64, generator=torch.Generator().manual_seed(0))
+
+    def loss_of(a):
+        r, al, _ = _full(a, sc, W, H, 3, render_mode=mode, background=torch.tensor([0.1, 0.2, 0.3], dtype=torch.float64))
+        return (r * v).sum() + 0.5 * al.sum()
+
+    leaves = {k: t.clone().requires_grad_(True) for k, t in act.items()}
+    loss_of(leaves).backward()
+    g = torch.Generator().manual_seed(1)
+    for k in leaves:
+        for _ in range(6):
+            idx = tuple(int(torch.randint(0, s, (1,), generator=g)) for s in leaves[k].shape)
+            eps = 1e-6
+            ap, am = {kk: t.clone() for kk, t in act.items()}, {kk: t.clone() for kk, t in act.items()}
+            ap[k][idx] += eps
+            am[k][idx] -= eps
+            fd = (loss_of(ap) - loss_of(am)).item() / (2 * eps)
+            an = leaves[k].grad[idx].item()
+            assert abs(fd - an) <= 1e-4 * max(1.0, abs(fd)), f"{k}{idx}: fd {fd} vs autograd {an}"
+
+
+# ---- C/OpenMP port against the PyTorch oracle ---------------------------------------------------------
+@pytest.mark.parametrize("N,W,H,deg", [(3000, 128, 80, 3), (6000, 200, 120, 1), (500, 40, 24, 0)])
+def test_c_port_matches_torch_oracle(N, W, H, deg):
+    sc, act = _scene(N, W, H, seed=7)
+    bg = torch.tensor([0.3, 0.1, 0.6])
+    fw = cpu_port.forward(act, sc["viewmat"], sc["K"], W, H, deg, bg=bg)
+    # binning: bit-exact given the port's own projection outputs
+    ob = orc.bin_tiles(fw["means2d"], fw["radii"], fw["depths"], W, H)
+    assert torch.equal(fw["tiles_per_gauss"], ob["tiles_per_gauss"])
+    ids_s, flat_s, offs = orc.sort_and_ranges(ob["isect_ids"], ob["flatten_ids"], ob["tile_w"], ob["tile_h"])
+    assert torch.equal(fw["isect_ids"], ids_s) and torch.equal(fw["flatten_ids"], flat_s)
+    assert torch.equal(fw["isect_offsets"], offs)
+    # full pipeline vs oracle
+    leaves = {k: t.clone().requires_grad_(True) for k, t in act.items()}
+    r_o, a_o, m_o = _full(leaves, sc, W, H, deg, background=bg, margin_eps=1e-3)
+    mism = (fw["radii"] != m_o["radii"]).any(-1).float().mean().item()
+    assert mism <= 2e-3
+    ok = ~m_o["marginal"]
+    assert (fw["render"] - r_o.detach()).abs().amax(-1)[ok].max() <= 1e-4
+    assert (fw["alpha"] - a_o.detach()).abs().amax(-1)[ok].max() <= 1e-4
+    v = torch.randn(H, W, 3, generator=torch.Generator().manual_seed(1))
+    (r_o * v).sum().backward()
+    grads = cpu_port.backward(fw, W, H, deg, v)
+    same = mism == 0
+    for k in leaves:
+        go = leaves[k].grad.reshape(grads[k].shape)
+        rel = ((grads[k] - go).norm() / go.norm().clamp_min(1e-12)).item()
+        assert rel <= (2e-3 if same else 3e-2), f"{k}: {rel}"
+
+
+def test_c_port_radix_sort_is_stable():
+    import ctypes as C
+    n = 200_003
+    g = torch.Generator().manual_seed(0)
+    keys = torch.randint(0, 2 ** 44, (n,), generator=g, dtype=torch.int64)
+    keys[: n // 2] &= 0xFFF
+    vals = torch.arange(n, dtype=torch.int32)
+    k, v = keys.clone(), vals.clone()
+    tk, tv = torch.empty_like(k), torch.empty_like(v)
+    cpu_port._lib.cpu_sort_pairs(cpu_port._p(k), cpu_port._p(v), cpu_port._p(tk), cpu_port._p(tv), C.c_int64(n), C.c_int(45))
+    order = torch.sort(keys, stable=True).indices
+    assert torch.equal(k, keys[order]) and torch.equal(v, vals[order])
+
+
+def test_densify_stats_port():
+    N = 1001
+    g = torch.Generator().manual_seed(0)
+    grad, a, c = torch.randn(N, 3, generator=g), torch.rand(N, 3, generator=g), torch.ones(N, 1)
+    a2, c2 = a.clone(), c.clone()
+    orc.densify_stats(a, c, grad)
+    cpu_port.densify_stats(a2, c2, grad)
+    assert torch.allclose(a, a2, rtol=1e-6) and torch.equal(c, c2)
+
+
+# ---- golden fixture (made by tests/golden/make_golden.py from the fp64 oracle) -------------------------
+def test_oracles_reproduce_the_committed_golden_fixture():
+    gold = torch.load(GOLDEN)
+    W, H, deg = gold["W"], gold["H"], gold["deg"]
+    act, sc = gold["act"], gold["scene"]
+    r, a, m = _full(act, sc, W, H, deg, background=gold["bg"], margin_eps=1e-3)
+    ok = ~m["marginal"]
+    assert (r - gold["render"]).abs().amax(-1)[ok].max() <= 1e-4
+    assert torch.equal(m["isect_ids"], gold["isect_ids"]) and torch.equal(m["flatten_ids"], gold["flatten_ids"])
+    assert torch.equal(m["isect_offsets"], gold["isect_offsets"])
+    fw = cpu_port.forward(act, sc["viewmat"], sc["K"], W, H, deg, bg=gold["bg"])
+    assert (fw["render"] - gold["render"]).abs().amax(-1)[ok].max() <= 1e-4
+    grads = cpu_port.backward(fw, W, H, deg, gold["v_render"])
+    for k, gref in gold["grads"].items():
+        rel = ((grads[k].reshape(gref.shape) - gref).norm() / gref.norm()).item()
+        assert rel <= 2e-3, f"{k}: {rel}"
