@@ -1,0 +1,79 @@
+// raster_common.cuh — shared pieces of the forward/backward blend kernels.
+//
+// Work decomposition (both directions): one WARP owns one half tile (16x8 px) of a 16x16 tile and
+// walks that tile's sorted list on its own — no block barriers.  The half tile is four 8x4 "slots";
+// lane l owns pixel (l & 7, l >> 3) of every slot, so a lane carries four pixels' state in registers
+// and a warp vote per slot skips sub-tiles a Gaussian does not reach.  Batches of 32 Gaussians are
+// gathered by the 32 lanes (three 16-B vectors per 48-B splat record), screened against the half
+// tile with an exact convex-quadratic bound, and only survivors are broadcast through shared memory.
+#pragma once
+#include "common.cuh"
+
+#define RU_WARPS 4                   // warps (= half-tile work units) per CTA
+#define RU_THREADS (RU_WARPS * 32)
+#define RU_SLOTS 4                   // 8x4 sub-tiles per half tile
+
+template <int CHSET> struct ChInfo;
+template <> struct ChInfo<B200_CH_RGB>  { static constexpr int CH = 3; };
+template <> struct ChInfo<B200_CH_D>    { static constexpr int CH = 1; };
+template <> struct ChInfo<B200_CH_RGBD> { static constexpr int CH = 4; };
+
+struct Bg { float v[4]; };
+
+struct __align__(16) StagedSplat {
+    float4 a;  // mx, my, A, B
+    float4 b;  // C, opacity, r, g
+    float2 c;  // b, depth
+    int id;    // Gaussian index
+    int idx;   // position in the sorted list
+};
+
+// sigma = 0.5*(A dx^2 + C dy^2) + B dx dy, with ONE fixed operation order shared by the forward and the
+// backward kernel so that both make the same skip decision for a (pixel, Gaussian) pair.
+__device__ __forceinline__ float eval_sigma(float hA, float B, float hC, float dx, float dy) {
+    float s = (hA * dx) * dx;
+    s = fmaf(hC * dy, dy, s);
+    s = fmaf(B * dx, dy, s);
+    return s;
+}
+
+// Conservative screen: can alpha = opacity * exp(-sigma) reach 1/255 anywhere on the pixel-centre
+// rectangle [x0,x1] x [y0,y1]?  The conic is positive definite, so sigma's minimum over the box is 0 if
+// the mean is inside, else it lies on one of the four edges where it is a clamped 1-D quadratic minimum.
+// A 1e-4 relative + absolute slack keeps every pair the exact per-pixel test could accept.
+__device__ __forceinline__ bool splat_reaches_box(const float4 a, const float4 b, float x0, float x1, float y0, float y1) {
+    const float mx = a.x, my = a.y, A = a.z, B = a.w, C = b.x, o = b.y;
+    const float dxl = mx - x1, dxh = mx - x0, dyl = my - y1, dyh = my - y0;  // d = mean - pixel
+    if (dxl <= 0.f && dxh >= 0.f && dyl <= 0.f && dyh >= 0.f) return true;
+    const float hA = 0.5f * A, hC = 0.5f * C;
+    const float rA = __fdividef(1.f, A), rC = __fdividef(1.f, C);
+    float smin;
+    {
+        float dy = fminf(fmaxf(-B * dxl * rC, dyl), dyh);
+        smin = eval_sigma(hA, B, hC, dxl, dy);
+        dy = fminf(fmaxf(-B * dxh * rC, dyl), dyh);
+        smin = fminf(smin, eval_sigma(hA, B, hC, dxh, dy));
+        float dx = fminf(fmaxf(-B * dyl * rA, dxl), dxh);
+        smin = fminf(smin, eval_sigma(hA, B, hC, dx, dyl));
+        dx = fminf(fmaxf(-B * dyh * rA, dxl), dxh);
+        smin = fminf(smin, eval_sigma(hA, B, hC, dx, dyh));
+    }
+    const float tau = __logf(255.f * o);  // alpha >= 1/255  <=>  sigma <= ln(255 o)
+    return !(smin > tau * 1.0001f + 1e-4f);
+}
+
+__device__ __forceinline__ float fast_rcp(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// 16-byte vector reduction into global memory (sm_90+): one RED for four adjacent floats.
+__device__ __forceinline__ void red_add_v4(float* addr, float x, float y, float z, float w) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+__device__ __forceinline__ void red_add_v2(float* addr, float x, float y) {
+    asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(x), "f"(y) : "memory");
+}
+
+int b200_channels(int chset);

@@ -1,90 +1,115 @@
-// raster_fwd.cu — stage 3: per-tile front-to-back alpha blend (gsplat
-// rasterize_to_pixels forward as reached from gsplat_backend.py:168-182).
-// One CTA per 16x16 tile; each batch of 256 sorted Gaussians is gathered (three 16-B vectors per
-// 48-B splat record, L2-resident: N*48 B < 126 MB up to 2.6 M Gaussians) into shared memory and
-// broadcast to the 256 pixel threads.
-#include "common.cuh"
-
-#define RF_THREADS (TILE * TILE)
+// raster_fwd.cu — stage 3: front-to-back alpha blend (gsplat rasterize_to_pixels
+// forward as reached from gsplat_backend.py:168-182).  Work decomposition: raster_common.cuh.
+#include "raster_common.cuh"
 
 namespace {
 
-template <int CHSET> struct ChInfo;
-template <> struct ChInfo<B200_CH_RGB>  { static constexpr int CH = 3; };
-template <> struct ChInfo<B200_CH_D>    { static constexpr int CH = 1; };
-template <> struct ChInfo<B200_CH_RGBD> { static constexpr int CH = 4; };
-
-struct Bg { float v[4]; };
-
 template <int CHSET>
-__global__ void __launch_bounds__(RF_THREADS)
+__global__ void __launch_bounds__(RU_THREADS)
 raster_fwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__ flatten_ids,
                   const int32_t* __restrict__ offsets, int M, int W, int H, int tile_w, int n_tiles, Bg bg,
                   float* __restrict__ render, float* __restrict__ alpha_out, int32_t* __restrict__ last_ids) {
     constexpr int CH = ChInfo<CHSET>::CH;
-    __shared__ float4 s_a[RF_THREADS];  // mx, my, A, B
-    __shared__ float4 s_b[RF_THREADS];  // C, opacity, r, g
-    __shared__ float2 s_c[RF_THREADS];  // b, depth
+    constexpr bool HAS_RGB = (CHSET != B200_CH_D);
+    constexpr bool HAS_D = (CHSET != B200_CH_RGB);
+    __shared__ StagedSplat s_splat[RU_WARPS][32];
 
-    const int tile = blockIdx.x;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int unit = blockIdx.x * RU_WARPS + wid;
+    if (unit >= 2 * n_tiles) return;
+    const int tile = unit >> 1, half = unit & 1;
     const int ty = tile / tile_w, tx = tile - ty * tile_w;
-    const int lx = threadIdx.x & (TILE - 1), ly = threadIdx.x >> 4;
-    const int ix = tx * TILE + lx, iy = ty * TILE + ly;
-    const bool inside = ix < W && iy < H;
-    const float px = (float)ix + 0.5f, py = (float)iy + 0.5f;
+    const int lx = lane & 7, ly = lane >> 3;
+    const int x_base = tx * TILE, y_base = ty * TILE + half * 8;
+    StagedSplat* stage = s_splat[wid];
 
+    float px[RU_SLOTS], py[RU_SLOTS], T[RU_SLOTS], acc[RU_SLOTS][CH];
+    int last[RU_SLOTS];
+    unsigned done = 0;  // bit s: pixel of slot s finished (or outside the image)
+#pragma unroll
+    for (int s = 0; s < RU_SLOTS; ++s) {
+        const int ix = x_base + (s & 1) * 8 + lx, iy = y_base + (s >> 1) * 4 + ly;
+        px[s] = (float)ix + 0.5f;
+        py[s] = (float)iy + 0.5f;
+        T[s] = 1.f;
+        last[s] = -1;
+#pragma unroll
+        for (int c = 0; c < CH; ++c) acc[s][c] = 0.f;
+        if (ix >= W || iy >= H) done |= 1u << s;
+    }
+    const float bx0 = (float)x_base + 0.5f, bx1 = (float)min(x_base + 15, W - 1) + 0.5f;
+    const float by0 = (float)y_base + 0.5f, by1 = (float)min(y_base + 7, H - 1) + 0.5f;
     const int start = offsets[tile];
     const int end = (tile + 1 < n_tiles) ? offsets[tile + 1] : M;
 
-    float T = 1.f;
-    float acc[CH];
-#pragma unroll
-    for (int c = 0; c < CH; ++c) acc[c] = 0.f;
-    int last = -1;
-    bool done = !inside;
-
-    for (int b0 = start; b0 < end; b0 += RF_THREADS) {
-        if (__syncthreads_count(done) == RF_THREADS) break;
-        const int idx = b0 + threadIdx.x;
-        if (idx < end) {
-            const int g = __ldg(flatten_ids + idx);
+    for (int lo = start; lo < end; lo += 32) {
+        if (__all_sync(0xffffffffu, done == (1u << RU_SLOTS) - 1u)) break;
+        const int idx_l = lo + lane;
+        bool keep = false;
+        if (idx_l < end) {
+            const int g = __ldg(flatten_ids + idx_l);
             const float4* rec = splats + 3 * (size_t)g;
-            float4 a = __ldg(rec), b = __ldg(rec + 1), c = __ldg(rec + 2);
-            s_a[threadIdx.x] = a;
-            s_b[threadIdx.x] = b;
-            s_c[threadIdx.x] = make_float2(c.x, c.y);
-        }
-        __syncthreads();
-        const int nb = min(RF_THREADS, end - b0);
-        if (!done) {
-            for (int j = 0; j < nb; ++j) {
-                const float4 a = s_a[j];
-                const float4 b = s_b[j];
-                const float dx = a.x - px, dy = a.y - py;
-                const float sigma = 0.5f * (a.z * dx * dx + b.x * dy * dy) + a.w * dx * dy;
-                const float vis = __expf(-sigma);
-                const float al = fminf(MAX_ALPHA, b.y * vis);
-                if (sigma < 0.f || al < ALPHA_THRESHOLD) continue;
-                const float Tn = T * (1.f - al);
-                if (Tn <= T_STOP) { done = true; break; }
-                const float w = al * T;
-                if (CHSET == B200_CH_RGB || CHSET == B200_CH_RGBD) {
-                    acc[0] += w * b.z; acc[1] += w * b.w; acc[2] += w * s_c[j].x;
-                    if (CHSET == B200_CH_RGBD) acc[3] += w * s_c[j].y;
-                } else {
-                    acc[0] += w * s_c[j].y;
-                }
-                last = b0 + j;
-                T = Tn;
+            const float4 a = __ldg(rec), b = __ldg(rec + 1), c = __ldg(rec + 2);
+            keep = splat_reaches_box(a, b, bx0, bx1, by0, by1);
+            if (keep) {
+                stage[lane].a = a;
+                stage[lane].b = b;
+                stage[lane].c = make_float2(c.x, c.y);
+                stage[lane].idx = idx_l;
             }
         }
-    }
-    if (inside) {
-        const size_t pix = (size_t)iy * W + ix;
+        unsigned mask = __ballot_sync(0xffffffffu, keep);
+        __syncwarp();
+        while (mask) {
+            const int j = __ffs(mask) - 1;
+            mask &= mask - 1;
+            const float4 a = stage[j].a;
+            const float4 b = stage[j].b;
+            const float hA = 0.5f * a.z, hC = 0.5f * b.x;
+            float al[RU_SLOTS];
+            unsigned act = 0, any = 0;
 #pragma unroll
-        for (int c = 0; c < CH; ++c) render[pix * CH + c] = acc[c] + T * bg.v[c];
-        alpha_out[pix] = 1.f - T;
-        last_ids[pix] = last;
+            for (int s = 0; s < RU_SLOTS; ++s) {
+                const float dx = a.x - px[s], dy = a.y - py[s];
+                const float sigma = eval_sigma(hA, a.w, hC, dx, dy);
+                const float vis = __expf(-sigma);
+                al[s] = fminf(MAX_ALPHA, b.y * vis);
+                const bool ok = !(done & (1u << s)) && sigma >= 0.f && al[s] >= ALPHA_THRESHOLD;
+                if (ok) act |= 1u << s;
+                if (__any_sync(0xffffffffu, ok)) any |= 1u << s;
+            }
+            if (!any) continue;
+            const float2 c2 = stage[j].c;
+            const int idx = stage[j].idx;
+#pragma unroll
+            for (int s = 0; s < RU_SLOTS; ++s) {
+                if (!(any & (1u << s))) continue;  // warp-uniform
+                if (act & (1u << s)) {
+                    const float Tn = T[s] * (1.f - al[s]);
+                    if (Tn <= T_STOP) {
+                        done |= 1u << s;
+                    } else {
+                        const float w = al[s] * T[s];
+                        if (HAS_RGB) { acc[s][0] += w * b.z; acc[s][1] += w * b.w; acc[s][2] += w * c2.x; }
+                        if (HAS_D) acc[s][CH - 1] += w * c2.y;
+                        last[s] = idx;
+                        T[s] = Tn;
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    }
+#pragma unroll
+    for (int s = 0; s < RU_SLOTS; ++s) {
+        const int ix = x_base + (s & 1) * 8 + lx, iy = y_base + (s >> 1) * 4 + ly;
+        if (ix < W && iy < H) {
+            const size_t pix = (size_t)iy * W + ix;
+#pragma unroll
+            for (int c = 0; c < CH; ++c) render[pix * CH + c] = acc[s][c] + T[s] * bg.v[c];
+            alpha_out[pix] = 1.f - T[s];
+            last_ids[pix] = last[s];
+        }
     }
 }
 
@@ -113,7 +138,8 @@ extern "C" int b200_raster_fwd(const float* splats, const int32_t* flatten_ids, 
     for (int c = 0; c < 4; ++c) bg.v[c] = (background_host && c < b200_channels(channels)) ? background_host[c] : 0.f;
     cudaStream_t st = (cudaStream_t)stream;
     const float4* sp = reinterpret_cast<const float4*>(splats);
-#define LAUNCH(CS) raster_fwd_kernel<CS><<<n_tiles, RF_THREADS, 0, st>>>(sp, flatten_ids, offsets, (int)M, width, height, tile_w, n_tiles, bg, render, alpha, last_ids)
+    const int grid = (2 * n_tiles + RU_WARPS - 1) / RU_WARPS;
+#define LAUNCH(CS) raster_fwd_kernel<CS><<<grid, RU_THREADS, 0, st>>>(sp, flatten_ids, offsets, (int)M, width, height, tile_w, n_tiles, bg, render, alpha, last_ids)
     switch (channels) {
         case B200_CH_RGB: LAUNCH(B200_CH_RGB); break;
         case B200_CH_D: LAUNCH(B200_CH_D); break;
