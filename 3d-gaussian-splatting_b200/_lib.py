@@ -30,7 +30,13 @@ SIGNATURES = {
     "b200_version": (C.c_int, []),
     "b200_last_error": (C.c_char_p, []),
     "b200_project_blocks": (_l, [_l]),
-    "b200_project_sh_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _i, _i, _p, _p, _p, _p, _p]),
+    "b200_project_sh_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p]),
+    "b200_sort_pairs_k32": (_i, [_p, _p, _p, _p, _l, _i, _p, _z, _p, _p]),
+    "b200_sort_pairs_k16": (_i, [_p, _p, _p, _p, _l, _i, _p, _z, _p, _p]),
+    "b200_bin_count_sorted": (_i, [_p, _p, _l, _p, _p]),
+    "b200_bin_emit_sorted": (_i, [_p, _p, _p, _p, _p, _l, _i, _i, _l, _p, _p, _p]),
+    "b200_tile_ranges_k16": (_i, [_p, _l, _i, _p, _p]),
+    "b200_isect_ids": (_i, [_p, _p, _p, _l, _p, _p]),
     "b200_bin_scan": (_i, [_p, _l, _p, _p, _p]),
     "b200_bin_emit": (_i, [_p, _p, _p, _p, _l, _i, _i, _l, _p, _p, _p, _p]),
     "b200_sort_scratch_bytes": (_z, [_l]),

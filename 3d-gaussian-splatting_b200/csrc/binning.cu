@@ -127,6 +127,108 @@ __global__ void tile_ranges_kernel(const int64_t* __restrict__ ids, int64_t M, i
         for (int t = cur + 1; t < n_tiles; ++t) offsets[t] = (int32_t)M;
 }
 
+// ---- split-key path: emission in DEPTH order (perm = Gaussian ids sorted by depth bits) -------------
+__global__ void __launch_bounds__(EMIT_THREADS)
+bin_count_sorted_kernel(const int32_t* __restrict__ tiles_per_gauss, const int32_t* __restrict__ perm, int64_t N,
+                        int64_t* __restrict__ block_sums) {
+    __shared__ int warp_tot[EMIT_THREADS / 32];
+    const int64_t i = (int64_t)blockIdx.x * EMIT_THREADS + threadIdx.x;
+    int v = (i < N) ? __ldg(tiles_per_gauss + __ldg(perm + i)) : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) warp_tot[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int64_t tot = 0;
+#pragma unroll
+        for (int w = 0; w < EMIT_THREADS / 32; ++w) tot += warp_tot[w];
+        block_sums[blockIdx.x] = tot;
+    }
+}
+
+__global__ void __launch_bounds__(EMIT_THREADS)
+bin_emit_sorted_kernel(const float* __restrict__ splats, const int32_t* __restrict__ radii,
+                       const int32_t* __restrict__ tiles_per_gauss, const int32_t* __restrict__ perm,
+                       const int64_t* __restrict__ block_offsets, int64_t N, int tile_w, int tile_h, int64_t M,
+                       uint16_t* __restrict__ tile_keys, int32_t* __restrict__ flatten_ids) {
+    __shared__ int s_excl[EMIT_THREADS + 1];
+    __shared__ int s_minx[EMIT_THREADS], s_miny[EMIT_THREADS], s_bw[EMIT_THREADS], s_g[EMIT_THREADS];
+    __shared__ int s_warp[EMIT_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int64_t i = (int64_t)blockIdx.x * EMIT_THREADS + tid;
+    int cnt = 0;
+    if (i < N) {
+        const int g = __ldg(perm + i);
+        cnt = __ldg(tiles_per_gauss + g);
+        if (cnt > 0) {
+            const float4 r0 = __ldg(reinterpret_cast<const float4*>(splats) + 3 * (size_t)g);
+            const int2 rad = __ldg(reinterpret_cast<const int2*>(radii) + g);
+            float tile_x = r0.x / (float)TILE, tile_y = r0.y / (float)TILE;
+            float trx = (float)rad.x / (float)TILE, try_ = (float)rad.y / (float)TILE;
+            float fw = (float)tile_w, fh = (float)tile_h;
+            int minx = (int)fminf(fmaxf(floorf(tile_x - trx), 0.f), fw);
+            int maxx = (int)fminf(fmaxf(ceilf(tile_x + trx), 0.f), fw);
+            int miny = (int)fminf(fmaxf(floorf(tile_y - try_), 0.f), fh);
+            s_minx[tid] = minx; s_miny[tid] = miny; s_bw[tid] = maxx - minx; s_g[tid] = g;
+        }
+    }
+    int inc = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    if (lane == 31) s_warp[wid] = inc;
+    __syncthreads();
+    int woff = 0;
+#pragma unroll
+    for (int w = 0; w < EMIT_THREADS / 32; ++w) woff += (w < wid) ? s_warp[w] : 0;
+    const int excl = woff + inc - cnt;
+    s_excl[tid] = excl;
+    if (tid == EMIT_THREADS - 1) s_excl[EMIT_THREADS] = excl + cnt;
+    const int64_t boff = block_offsets[blockIdx.x];
+    __syncthreads();
+    const int total = s_excl[EMIT_THREADS];
+    for (int k = tid; k < total; k += EMIT_THREADS) {
+        int lo = 0, hi = EMIT_THREADS;
+        while (hi - lo > 1) {
+            int mid = (lo + hi) >> 1;
+            if (s_excl[mid] <= k) lo = mid; else hi = mid;
+        }
+        const int kk = k - s_excl[lo];
+        const int bw = s_bw[lo];
+        const int ty = s_miny[lo] + kk / bw, tx = s_minx[lo] + kk % bw;
+        const int64_t out = boff + k;
+        if (out < M) {
+            tile_keys[out] = (uint16_t)(ty * tile_w + tx);
+            flatten_ids[out] = s_g[lo];
+        }
+    }
+}
+
+__global__ void tile_ranges_k16_kernel(const uint16_t* __restrict__ keys, int64_t M, int n_tiles, int32_t* __restrict__ offsets) {
+    int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= M) return;
+    int cur = (int)keys[idx];
+    if (idx == 0) {
+        for (int t = 0; t <= cur; ++t) offsets[t] = 0;
+    } else {
+        int prev = (int)keys[idx - 1];
+        for (int t = prev + 1; t <= cur; ++t) offsets[t] = (int32_t)idx;
+    }
+    if (idx == M - 1)
+        for (int t = cur + 1; t < n_tiles; ++t) offsets[t] = (int32_t)M;
+}
+
+// sorted 64-bit keys of the literal formulation, rebuilt on request (parity tests / gsplat meta)
+__global__ void isect_ids_kernel(const uint16_t* __restrict__ tile_keys, const int32_t* __restrict__ flatten_ids,
+                                 const float* __restrict__ splats, int64_t M, int64_t* __restrict__ isect_ids) {
+    int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= M) return;
+    const uint32_t db = __float_as_uint(__ldg(splats + (size_t)flatten_ids[idx] * SPLAT_F + 9));
+    isect_ids[idx] = ((int64_t)tile_keys[idx] << 32) | (int64_t)db;
+}
+
 }  // namespace
 
 extern "C" int b200_bin_scan(const int64_t* block_sums, int64_t nblocks, int64_t* block_offsets, int64_t* total, void* stream) {
@@ -160,4 +262,49 @@ extern "C" int b200_tile_ranges(const int64_t* sorted_isect_ids, int64_t M, int 
     B200_REQUIRE(sorted_isect_ids, "null pointer");
     tile_ranges_kernel<<<(unsigned)((M + 255) / 256), 256, 0, st>>>(sorted_isect_ids, M, n_tiles, offsets);
     return b200_check_launch("tile_ranges");
+}
+
+extern "C" int b200_bin_count_sorted(const int32_t* tiles_per_gauss, const int32_t* perm, int64_t N, int64_t* block_sums,
+                                     void* stream) {
+    B200_REQUIRE(N >= 0, "bad size");
+    if (N == 0) return B200_OK;
+    B200_REQUIRE(tiles_per_gauss && perm && block_sums, "null pointer");
+    bin_count_sorted_kernel<<<(unsigned)b200_project_blocks(N), EMIT_THREADS, 0, (cudaStream_t)stream>>>(tiles_per_gauss, perm, N, block_sums);
+    return b200_check_launch("bin_count_sorted");
+}
+
+extern "C" int b200_bin_emit_sorted(const float* splats, const int32_t* radii, const int32_t* tiles_per_gauss,
+                                    const int32_t* perm, const int64_t* block_offsets, int64_t N, int width, int height,
+                                    int64_t M, uint16_t* tile_keys, int32_t* flatten_ids, void* stream) {
+    B200_REQUIRE(N >= 0 && M >= 0 && width > 0 && height > 0, "bad sizes");
+    B200_REQUIRE(M < ((int64_t)1 << 30), "too many intersections (M >= 2^30)");
+    int tile_w = (width + TILE - 1) / TILE, tile_h = (height + TILE - 1) / TILE;
+    B200_REQUIRE((int64_t)tile_w * tile_h <= 65536, "more than 65536 tiles: use the 64-bit key path");
+    if (N == 0) return B200_OK;
+    B200_REQUIRE(splats && radii && tiles_per_gauss && perm && block_offsets, "null pointer");
+    B200_REQUIRE(M == 0 || (tile_keys && flatten_ids), "null output");
+    bin_emit_sorted_kernel<<<(unsigned)b200_project_blocks(N), EMIT_THREADS, 0, (cudaStream_t)stream>>>(
+        splats, radii, tiles_per_gauss, perm, block_offsets, N, tile_w, tile_h, M, tile_keys, flatten_ids);
+    return b200_check_launch("bin_emit_sorted");
+}
+
+extern "C" int b200_tile_ranges_k16(const uint16_t* sorted_tile_keys, int64_t M, int n_tiles, int32_t* offsets, void* stream) {
+    B200_REQUIRE(M >= 0 && n_tiles > 0 && n_tiles <= 65536 && offsets, "bad args");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (M == 0) {
+        cudaMemsetAsync(offsets, 0, sizeof(int32_t) * (size_t)n_tiles, st);
+        return b200_check_launch("tile_ranges_k16(memset)");
+    }
+    B200_REQUIRE(sorted_tile_keys, "null pointer");
+    tile_ranges_k16_kernel<<<(unsigned)((M + 255) / 256), 256, 0, st>>>(sorted_tile_keys, M, n_tiles, offsets);
+    return b200_check_launch("tile_ranges_k16");
+}
+
+extern "C" int b200_isect_ids(const uint16_t* sorted_tile_keys, const int32_t* flatten_ids, const float* splats, int64_t M,
+                              int64_t* isect_ids, void* stream) {
+    B200_REQUIRE(M >= 0, "bad size");
+    if (M == 0) return B200_OK;
+    B200_REQUIRE(sorted_tile_keys && flatten_ids && splats && isect_ids, "null pointer");
+    isect_ids_kernel<<<(unsigned)((M + 255) / 256), 256, 0, (cudaStream_t)stream>>>(sorted_tile_keys, flatten_ids, splats, M, isect_ids);
+    return b200_check_launch("isect_ids");
 }

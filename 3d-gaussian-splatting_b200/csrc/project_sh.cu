@@ -162,7 +162,8 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
                       const float* __restrict__ scales, const float* __restrict__ opacities,
                       const float* __restrict__ shs, int sh_coeffs, bool vec_ok, int64_t N, Cam cam,
                       int32_t* __restrict__ radii, float* __restrict__ splats,
-                      int32_t* __restrict__ tiles_per_gauss, int64_t* __restrict__ block_sums) {
+                      int32_t* __restrict__ tiles_per_gauss, int64_t* __restrict__ block_sums,
+                      uint32_t* __restrict__ depth_keys, int32_t* __restrict__ gauss_ids) {
     int64_t g = (int64_t)blockIdx.x * PROJ_THREADS + threadIdx.x;
     int ntiles = 0;
     if (g < N) {
@@ -216,6 +217,10 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
         float4* rec = reinterpret_cast<float4*>(splats) + 3 * g;
         rec[0] = r0; rec[1] = r1; rec[2] = r2;
         tiles_per_gauss[g] = ntiles;
+        if (depth_keys != nullptr) {  // split-key sort: depth digits are sorted over Gaussians, before duplication
+            depth_keys[g] = ntiles > 0 ? __float_as_uint(r2.y) : 0xFFFFFFFFu;
+            gauss_ids[g] = (int32_t)g;
+        }
     }
     // block sum of tile counts (feeds b200_bin_scan)
     __shared__ int warp_tot[PROJ_THREADS / 32];
@@ -422,17 +427,19 @@ static bool sh_args_ok(int sh_coeffs, int sh_degree) {
 extern "C" int b200_project_sh_fwd(const float* means, const float* quats, const float* scales,
                                    const float* opacities, const float* shs, int sh_coeffs, int sh_degree,
                                    int64_t N, const float* cam_host, int width, int height, int32_t* radii,
-                                   float* splats, int32_t* tiles_per_gauss, int64_t* block_sums, void* stream) {
+                                   float* splats, int32_t* tiles_per_gauss, int64_t* block_sums,
+                                   uint32_t* depth_keys, int32_t* gauss_ids, void* stream) {
     B200_REQUIRE(N >= 0 && width > 0 && height > 0, "bad sizes");
     B200_REQUIRE(sh_args_ok(sh_coeffs, sh_degree), "sh_degree/sh_coeffs mismatch");
     if (N == 0) return B200_OK;
     B200_REQUIRE(means && quats && scales && opacities && shs && cam_host && radii && splats && tiles_per_gauss && block_sums, "null pointer");
     B200_REQUIRE(((uintptr_t)quats & 15) == 0 && ((uintptr_t)splats & 15) == 0 && ((uintptr_t)radii & 7) == 0, "misaligned pointer");
+    B200_REQUIRE((depth_keys == nullptr) == (gauss_ids == nullptr), "depth_keys and gauss_ids go together");
     Cam cam = b200_make_cam(cam_host, width, height);
     bool vec_ok = sh_degree >= 0 && ((sh_coeffs * 12) % 16 == 0) && (((uintptr_t)shs & 15) == 0);
     dim3 grid((unsigned)b200_project_blocks(N)), block(PROJ_THREADS);
     cudaStream_t st = (cudaStream_t)stream;
-#define LAUNCH(D) project_sh_fwd_kernel<D><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, cam, radii, splats, tiles_per_gauss, block_sums)
+#define LAUNCH(D) project_sh_fwd_kernel<D><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, cam, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids)
     switch (sh_degree) {
         case 0: LAUNCH(0); break;
         case 1: LAUNCH(1); break;

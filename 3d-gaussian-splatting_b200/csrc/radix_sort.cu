@@ -1,8 +1,13 @@
-// radix_sort.cu — stage 2c: stable LSD radix sort of (uint64 key, uint32 value) pairs, 8-bit digits,
+// radix_sort.cu — stage 2c: stable LSD radix sort of (key, uint32 value) pairs, 8-bit digits,
 // single-read "onesweep" passes with decoupled look-back between tiles.  Replaces the
 // cub::DeviceRadixSort::SortPairs call inside gsplat isect_tiles(sort=True) that the reference reaches
 // through gsplat_backend.py:168-182.  Stability (ties keep emission order) comes from
 // in-order ranking inside a warp, warp-major order inside a tile and ticket order between tiles.
+//
+// Three key widths share one kernel template: 64-bit (tile<<32 | depth) keys of the literal gsplat
+// formulation, and the split form the fast path uses — 32-bit depth keys over Gaussians BEFORE tile
+// duplication followed by 16-bit tile keys over intersections (the same LSD digit order, with the
+// duplication moved between the depth digits and the tile digits; see DESIGN.md "Sort").
 #include "common.cuh"
 
 #define RS_BITS 8
@@ -12,6 +17,7 @@
 #define RS_ITEMS 16
 #define RS_TILE (RS_THREADS * RS_ITEMS)
 #define RS_MAX_PASSES 8
+#define RS_LOOKBACK 8  // predecessor status words fetched per look-back step (memory-level parallelism)
 
 #define FLAG_AGG 0x40000000u
 #define FLAG_PREFIX 0x80000000u
@@ -21,8 +27,9 @@
 namespace {
 
 // All per-pass digit histograms in one read of the keys.
+template <typename KeyT>
 __global__ void __launch_bounds__(256)
-rs_hist_kernel(const uint64_t* __restrict__ keys, int64_t n, int npasses, int end_bit, uint32_t* __restrict__ hist) {
+rs_hist_kernel(const KeyT* __restrict__ keys, int64_t n, int npasses, int end_bit, uint32_t* __restrict__ hist) {
     __shared__ uint32_t s_hist[RS_MAX_PASSES * RS_RADIX];
     for (int i = threadIdx.x; i < npasses * RS_RADIX; i += blockDim.x) s_hist[i] = 0;
     __syncthreads();
@@ -31,7 +38,7 @@ rs_hist_kernel(const uint64_t* __restrict__ keys, int64_t n, int npasses, int en
     const int64_t n_round = (n + 31) / 32 * 32;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
         const bool valid = i < n;
-        const uint64_t k = valid ? keys[i] : 0;
+        const uint64_t k = valid ? (uint64_t)keys[i] : 0;
         const unsigned act = __ballot_sync(0xffffffffu, valid);
         if (valid) {
             for (int p = 0; p < npasses; ++p) {
@@ -68,8 +75,9 @@ rs_scan_kernel(uint32_t* __restrict__ hist) {
     h[threadIdx.x] = off + inc - v;
 }
 
+template <typename KeyT>
 struct __align__(16) RsSmem {
-    uint64_t keys[RS_TILE];
+    KeyT keys[RS_TILE];
     uint32_t vals[RS_TILE];
     uint32_t warp_hist[RS_WARPS][RS_RADIX];  // per-warp digit counts -> exclusive offsets across warps
     uint32_t bin_excl[RS_RADIX];             // tile-local exclusive start of each digit
@@ -78,13 +86,14 @@ struct __align__(16) RsSmem {
     uint32_t tile;
 };
 
+template <typename KeyT>
 __global__ void __launch_bounds__(RS_THREADS)
-rs_onesweep_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                   uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n, int shift, int bits,
+rs_onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                   KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n, int shift, int bits,
                    const uint32_t* __restrict__ digit_base, volatile uint32_t* __restrict__ status,
                    uint32_t* __restrict__ ticket) {
     extern __shared__ __align__(16) unsigned char rs_smem_raw[];
-    RsSmem& S = *reinterpret_cast<RsSmem*>(rs_smem_raw);
+    RsSmem<KeyT>& S = *reinterpret_cast<RsSmem<KeyT>*>(rs_smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const uint32_t dmask = (1u << bits) - 1u;
 
@@ -96,7 +105,7 @@ rs_onesweep_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restr
     const int n_valid = (int)min((int64_t)RS_TILE, n - tile_base);
 
     // ---- load (warp-striped so that order inside a warp is item-major, lane-minor) ----
-    uint64_t key[RS_ITEMS];
+    KeyT key[RS_ITEMS];
     uint32_t val[RS_ITEMS];
     uint32_t pos[RS_ITEMS];
     const int warp_base = wid * (32 * RS_ITEMS);
@@ -104,14 +113,14 @@ rs_onesweep_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restr
     for (int i = 0; i < RS_ITEMS; ++i) {
         int local = warp_base + i * 32 + lane;
         bool ok = local < n_valid;
-        key[i] = ok ? keys_in[tile_base + local] : ~0ull;
+        key[i] = ok ? keys_in[tile_base + local] : (KeyT)~(KeyT)0;
         val[i] = ok ? vals_in[tile_base + local] : 0u;
     }
     // ---- rank inside the warp by digit, in order ----
     const unsigned lt_mask = (1u << lane) - 1u;
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; ++i) {
-        uint32_t d = (uint32_t)(key[i] >> shift) & dmask;
+        uint32_t d = (uint32_t)((uint64_t)key[i] >> shift) & dmask;
         unsigned peers = __match_any_sync(0xffffffffu, d);
         int leader = __ffs(peers) - 1;
         uint32_t base = 0;
@@ -136,6 +145,10 @@ rs_onesweep_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restr
         }
         count = run;
     }
+    // publish this tile's aggregate as early as possible: successors can already add it
+    volatile uint32_t* my = status + (size_t)tile * RS_RADIX + tid;
+    *my = count | (tile == 0 ? FLAG_PREFIX : FLAG_AGG);
+
     // exclusive scan of counts over digits
     uint32_t inc = count;
 #pragma unroll
@@ -151,21 +164,24 @@ rs_onesweep_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restr
     const uint32_t excl_local = woff + inc - count;
     S.bin_excl[tid] = excl_local;
 
-    // ---- decoupled look-back over previous tiles for this digit ----
+    // ---- decoupled look-back: RS_LOOKBACK predecessors per step, consumed nearest-first ----
     {
-        volatile uint32_t* my = status + (size_t)tile * RS_RADIX + tid;
         uint32_t excl = 0;
-        if (tile == 0) {
-            *my = count | FLAG_PREFIX;
-        } else {
-            *my = count | FLAG_AGG;
+        if (tile != 0) {
             int64_t t = (int64_t)tile - 1;
-            while (true) {
-                uint32_t s = status[(size_t)t * RS_RADIX + tid];
-                if ((s & FLAG_MASK) == 0) continue;  // not published yet
-                excl += s & VAL_MASK;
-                if (s & FLAG_PREFIX) break;
-                --t;
+            bool found = false;
+            while (!found) {
+                uint32_t s[RS_LOOKBACK];
+#pragma unroll
+                for (int k = 0; k < RS_LOOKBACK; ++k) s[k] = (t - k >= 0) ? status[(size_t)(t - k) * RS_RADIX + tid] : FLAG_PREFIX;
+#pragma unroll
+                for (int k = 0; k < RS_LOOKBACK; ++k) {
+                    if (found) break;
+                    if ((s[k] & FLAG_MASK) == 0) break;  // not published yet: re-read from here
+                    excl += s[k] & VAL_MASK;
+                    --t;
+                    if (s[k] & FLAG_PREFIX) found = true;
+                }
             }
             *my = (excl + count) | FLAG_PREFIX;
         }
@@ -175,7 +191,7 @@ rs_onesweep_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restr
     // ---- scatter into tile-local sorted order ----
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; ++i) {
-        uint32_t d = (uint32_t)(key[i] >> shift) & dmask;
+        uint32_t d = (uint32_t)((uint64_t)key[i] >> shift) & dmask;
         uint32_t p = S.bin_excl[d] + S.warp_hist[wid][d] + pos[i];
         S.keys[p] = key[i];
         S.vals[p] = val[i];
@@ -186,8 +202,8 @@ rs_onesweep_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restr
     for (int i = 0; i < RS_ITEMS; ++i) {
         int p = i * RS_THREADS + tid;
         if (p < n_valid) {
-            uint64_t k = S.keys[p];
-            uint32_t d = (uint32_t)(k >> shift) & dmask;
+            KeyT k = S.keys[p];
+            uint32_t d = (uint32_t)((uint64_t)k >> shift) & dmask;
             int64_t o = S.global_off[d] + p;
             keys_out[o] = k;
             vals_out[o] = S.vals[p];
@@ -196,6 +212,55 @@ rs_onesweep_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restr
 }
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+template <typename KeyT>
+int sort_pairs_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_t* vals_b, int64_t M, int end_bit,
+                    void* scratch, size_t scratch_bytes, int* result_in_b_host, void* stream, const char* what) {
+    if (!(M >= 0 && end_bit > 0 && end_bit <= (int)(8 * sizeof(KeyT)))) {
+        b200_set_error("%s: bad sizes", what);
+        return B200_EARG;
+    }
+    if (M >= ((int64_t)1 << 30)) {
+        b200_set_error("%s: M >= 2^30 not supported", what);
+        return B200_EARG;
+    }
+    const int npasses = (end_bit + RS_BITS - 1) / RS_BITS;
+    if (result_in_b_host) *result_in_b_host = (M > 0) ? (npasses & 1) : 0;
+    if (M == 0) return B200_OK;
+    if (!(keys_a && vals_a && keys_b && vals_b && scratch)) {
+        b200_set_error("%s: null pointer", what);
+        return B200_EARG;
+    }
+    if (scratch_bytes < b200_sort_scratch_bytes(M)) {
+        b200_set_error("%s: scratch too small (%zu < %zu)", what, scratch_bytes, b200_sort_scratch_bytes(M));
+        return B200_ESCRATCH;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    static bool attr_set = false;  // one flag per template instantiation
+    if (!attr_set) {
+        cudaFuncSetAttribute(rs_onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem<KeyT>));
+        attr_set = true;
+    }
+    const size_t ntiles = (size_t)((M + RS_TILE - 1) / RS_TILE);
+    uint32_t* hist = reinterpret_cast<uint32_t*>(scratch);
+    uint32_t* tickets = hist + RS_MAX_PASSES * RS_RADIX;
+    uint32_t* status = tickets + 64;
+    const size_t used = (RS_MAX_PASSES * RS_RADIX + 64) * sizeof(uint32_t) + (size_t)npasses * ntiles * RS_RADIX * sizeof(uint32_t);
+    cudaMemsetAsync(scratch, 0, used, st);
+    int hist_blocks = (int)min((int64_t)148 * 8, (M + 255) / 256);
+    rs_hist_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_a, M, npasses, end_bit, hist);
+    rs_scan_kernel<<<npasses, RS_RADIX, 0, st>>>(hist);
+    KeyT* kin = keys_a; uint32_t* vin = vals_a; KeyT* kout = keys_b; uint32_t* vout = vals_b;
+    for (int p = 0; p < npasses; ++p) {
+        int shift = p * RS_BITS;
+        int bits = (end_bit - shift) < RS_BITS ? (end_bit - shift) : RS_BITS;
+        rs_onesweep_kernel<KeyT><<<(unsigned)ntiles, RS_THREADS, sizeof(RsSmem<KeyT>), st>>>(
+            kin, vin, kout, vout, M, shift, bits, hist + p * RS_RADIX, status + (size_t)p * ntiles * RS_RADIX, tickets + p);
+        KeyT* tk = kin; kin = kout; kout = tk;
+        uint32_t* tv = vin; vin = vout; vout = tv;
+    }
+    return b200_check_launch(what);
+}
 
 }  // namespace
 
@@ -210,39 +275,15 @@ extern "C" size_t b200_sort_scratch_bytes(int64_t M) {
 
 extern "C" int b200_sort_pairs(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, int64_t M,
                                int end_bit, void* scratch, size_t scratch_bytes, int* result_in_b_host, void* stream) {
-    B200_REQUIRE(M >= 0 && end_bit > 0 && end_bit <= 64, "bad sizes");
-    B200_REQUIRE(M < ((int64_t)1 << 30), "M >= 2^30 not supported");
-    const int npasses = (end_bit + RS_BITS - 1) / RS_BITS;
-    if (result_in_b_host) *result_in_b_host = (M > 0) ? (npasses & 1) : 0;
-    if (M == 0) return B200_OK;
-    B200_REQUIRE(keys_a && vals_a && keys_b && vals_b && scratch, "null pointer");
-    if (scratch_bytes < b200_sort_scratch_bytes(M)) {
-        b200_set_error("b200_sort_pairs: scratch too small (%zu < %zu)", scratch_bytes, b200_sort_scratch_bytes(M));
-        return B200_ESCRATCH;
-    }
-    cudaStream_t st = (cudaStream_t)stream;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(rs_onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem));
-        attr_set = true;
-    }
-    const size_t ntiles = (size_t)((M + RS_TILE - 1) / RS_TILE);
-    uint32_t* hist = reinterpret_cast<uint32_t*>(scratch);
-    uint32_t* tickets = hist + RS_MAX_PASSES * RS_RADIX;
-    uint32_t* status = tickets + 64;
-    const size_t used = (RS_MAX_PASSES * RS_RADIX + 64) * sizeof(uint32_t) + (size_t)npasses * ntiles * RS_RADIX * sizeof(uint32_t);
-    cudaMemsetAsync(scratch, 0, used, st);
-    int hist_blocks = (int)min((int64_t)148 * 8, (M + 255) / 256);
-    rs_hist_kernel<<<hist_blocks, 256, 0, st>>>(keys_a, M, npasses, end_bit, hist);
-    rs_scan_kernel<<<npasses, RS_RADIX, 0, st>>>(hist);
-    uint64_t* kin = keys_a; uint32_t* vin = vals_a; uint64_t* kout = keys_b; uint32_t* vout = vals_b;
-    for (int p = 0; p < npasses; ++p) {
-        int shift = p * RS_BITS;
-        int bits = (end_bit - shift) < RS_BITS ? (end_bit - shift) : RS_BITS;
-        rs_onesweep_kernel<<<(unsigned)ntiles, RS_THREADS, sizeof(RsSmem), st>>>(
-            kin, vin, kout, vout, M, shift, bits, hist + p * RS_RADIX, status + (size_t)p * ntiles * RS_RADIX, tickets + p);
-        uint64_t* tk = kin; kin = kout; kout = tk;
-        uint32_t* tv = vin; vin = vout; vout = tv;
-    }
-    return b200_check_launch("sort_pairs");
+    return sort_pairs_impl<uint64_t>(keys_a, vals_a, keys_b, vals_b, M, end_bit, scratch, scratch_bytes, result_in_b_host, stream, "b200_sort_pairs");
+}
+
+extern "C" int b200_sort_pairs_k32(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b, int64_t M,
+                                   int end_bit, void* scratch, size_t scratch_bytes, int* result_in_b_host, void* stream) {
+    return sort_pairs_impl<uint32_t>(keys_a, vals_a, keys_b, vals_b, M, end_bit, scratch, scratch_bytes, result_in_b_host, stream, "b200_sort_pairs_k32");
+}
+
+extern "C" int b200_sort_pairs_k16(uint16_t* keys_a, uint32_t* vals_a, uint16_t* keys_b, uint32_t* vals_b, int64_t M,
+                                   int end_bit, void* scratch, size_t scratch_bytes, int* result_in_b_host, void* stream) {
+    return sort_pairs_impl<uint16_t>(keys_a, vals_a, keys_b, vals_b, M, end_bit, scratch, scratch_bytes, result_in_b_host, stream, "b200_sort_pairs_k16");
 }

@@ -77,14 +77,26 @@ def tile_n_bits(tile_w: int, tile_h: int) -> int:
     return int(math.floor(math.log2(tile_w * tile_h))) + 1
 
 
+def _sort_scratch(M: int, dev) -> torch.Tensor:
+    return torch.empty(max(int(lib.b200_sort_scratch_bytes(M)), 256), dtype=torch.uint8, device=dev)
+
+
 def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional[int], cam, width: int,
-                    height: int, keep_unsorted: bool = False) -> Dict[str, torch.Tensor]:
-    """Stages 1-2 (projection+SH, tile binning, radix sort, tile ranges).  One host sync (reads M)."""
+                    height: int, keep_unsorted: bool = False, method: str = "auto",
+                    with_isect_ids: bool = False) -> Dict[str, torch.Tensor]:
+    """Stages 1-2 (projection+SH, tile binning, radix sort, tile ranges).  One host sync (reads M).
+
+    method "keys64": literal gsplat formulation — emit (tile<<32|depth) int64 keys, sort M pairs.
+    method "split" (default when tile_w*tile_h <= 65536): same result, depth digits sorted over the N
+    Gaussians before duplication, 16-bit tile digits over the M intersections (include/b200splat.h).
+    """
     dev = means.device
     N = means.shape[0]
     tile_w = (width + _lib.TILE - 1) // _lib.TILE
     tile_h = (height + _lib.TILE - 1) // _lib.TILE
     n_tiles = tile_w * tile_h
+    if method == "auto":
+        method = "split" if (n_tiles <= 65536 and not keep_unsorted) else "keys64"
     st = _stream()
     if sh_degree is None:
         sh_coeffs, deg = 1, -1
@@ -97,37 +109,87 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
     block_sums = torch.empty(max(nblocks, 1), dtype=torch.int64, device=dev)
     block_offsets = torch.empty(max(nblocks, 1), dtype=torch.int64, device=dev)
     total = torch.zeros(1, dtype=torch.int64, device=dev)
+    split = method == "split"
+    if split:
+        dkeys_a = torch.empty(max(N, 1), dtype=torch.int32, device=dev)
+        gids_a = torch.empty(max(N, 1), dtype=torch.int32, device=dev)
     with _stage("project_sh_fwd"):
         check(lib.b200_project_sh_fwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors),
                                       sh_coeffs, deg, N, cam, width, height, _ptr(radii), _ptr(splats),
-                                      _ptr(tiles_per_gauss), _ptr(block_sums), st), "b200_project_sh_fwd")
+                                      _ptr(tiles_per_gauss), _ptr(block_sums),
+                                      _ptr(dkeys_a) if split else None, _ptr(gids_a) if split else None, st),
+              "b200_project_sh_fwd", kernels=1 if N > 0 else 0)
+    out = dict(radii=radii, splats=splats, tiles_per_gauss=tiles_per_gauss, tile_w=tile_w, tile_h=tile_h)
+    offsets = torch.empty(n_tiles, dtype=torch.int32, device=dev)
+    in_b = C.c_int(0)
+    if not split:
+        with _stage("bin_scan"):
+            check(lib.b200_bin_scan(_ptr(block_sums), nblocks, _ptr(block_offsets), _ptr(total), st), "b200_bin_scan")
+        M = int(total.item())  # the one device->host sync of the forward pass (sizes the key buffers)
+        keys_a = torch.empty(max(M, 1), dtype=torch.int64, device=dev)
+        vals_a = torch.empty(max(M, 1), dtype=torch.int32, device=dev)
+        with _stage("bin_emit"):
+            check(lib.b200_bin_emit(_ptr(splats), _ptr(radii), _ptr(tiles_per_gauss), _ptr(block_offsets), N, width,
+                                    height, M, _ptr(keys_a), _ptr(vals_a), None, st), "b200_bin_emit",
+                  kernels=1 if N > 0 else 0)
+        if keep_unsorted:
+            out["isect_ids_unsorted"] = keys_a[:M].clone()
+            out["flatten_ids_unsorted"] = vals_a[:M].clone()
+        keys_b = torch.empty_like(keys_a)
+        vals_b = torch.empty_like(vals_a)
+        scratch = _sort_scratch(M, dev)
+        end_bit = 32 + tile_n_bits(tile_w, tile_h)
+        with _stage("sort_pairs"):
+            check(lib.b200_sort_pairs(_ptr(keys_a), _ptr(vals_a), _ptr(keys_b), _ptr(vals_b), M, end_bit,
+                                      _ptr(scratch), scratch.numel(), C.byref(in_b), st), "b200_sort_pairs",
+                  kernels=(2 + (end_bit + 7) // 8) if M > 0 else 0)
+        keys_s, vals_s = (keys_b, vals_b) if in_b.value else (keys_a, vals_a)
+        with _stage("tile_ranges"):
+            check(lib.b200_tile_ranges(_ptr(keys_s), M, n_tiles, _ptr(offsets), st), "b200_tile_ranges",
+                  kernels=1 if M > 0 else 0)
+        out.update(M=M, isect_ids=keys_s[:M], flatten_ids=vals_s[:M], isect_offsets=offsets.view(tile_h, tile_w))
+        return out
+
+    # ---- split-key path ----
+    dkeys_b = torch.empty_like(dkeys_a)
+    gids_b = torch.empty_like(gids_a)
+    scratch_n = _sort_scratch(N, dev)
+    with _stage("sort_depth"):
+        check(lib.b200_sort_pairs_k32(_ptr(dkeys_a), _ptr(gids_a), _ptr(dkeys_b), _ptr(gids_b), N, 32,
+                                      _ptr(scratch_n), scratch_n.numel(), C.byref(in_b), st), "b200_sort_pairs_k32",
+              kernels=6 if N > 0 else 0)
+    perm = gids_b if in_b.value else gids_a
     with _stage("bin_scan"):
+        check(lib.b200_bin_count_sorted(_ptr(tiles_per_gauss), _ptr(perm), N, _ptr(block_sums), st),
+              "b200_bin_count_sorted", kernels=1 if N > 0 else 0)
         check(lib.b200_bin_scan(_ptr(block_sums), nblocks, _ptr(block_offsets), _ptr(total), st), "b200_bin_scan")
-    M = int(total.item())  # the one device->host sync of the forward pass (sizes the key buffers)
-    keys_a = torch.empty(max(M, 1), dtype=torch.int64, device=dev)
+    M = int(total.item())  # the one device->host sync of the forward pass (sizes the intersection buffers)
+    tkeys_a = torch.empty(max(M, 1), dtype=torch.int16, device=dev)
     vals_a = torch.empty(max(M, 1), dtype=torch.int32, device=dev)
     with _stage("bin_emit"):
-        check(lib.b200_bin_emit(_ptr(splats), _ptr(radii), _ptr(tiles_per_gauss), _ptr(block_offsets), N, width,
-                                height, M, _ptr(keys_a), _ptr(vals_a), None, st), "b200_bin_emit")
-    out = dict(radii=radii, splats=splats, tiles_per_gauss=tiles_per_gauss, M=M, tile_w=tile_w, tile_h=tile_h)
-    if keep_unsorted:
-        out["isect_ids_unsorted"] = keys_a[:M].clone()
-        out["flatten_ids_unsorted"] = vals_a[:M].clone()
-    keys_b = torch.empty_like(keys_a)
+        check(lib.b200_bin_emit_sorted(_ptr(splats), _ptr(radii), _ptr(tiles_per_gauss), _ptr(perm),
+                                       _ptr(block_offsets), N, width, height, M, _ptr(tkeys_a), _ptr(vals_a), st),
+              "b200_bin_emit_sorted", kernels=1 if N > 0 else 0)
+    tkeys_b = torch.empty_like(tkeys_a)
     vals_b = torch.empty_like(vals_a)
-    sbytes = int(lib.b200_sort_scratch_bytes(M))
-    scratch = torch.empty(max(sbytes, 256), dtype=torch.uint8, device=dev)
-    in_b = C.c_int(0)
-    end_bit = 32 + tile_n_bits(tile_w, tile_h)
+    scratch_m = _sort_scratch(M, dev)
+    tbits = tile_n_bits(tile_w, tile_h)
     with _stage("sort_pairs"):
-        check(lib.b200_sort_pairs(_ptr(keys_a), _ptr(vals_a), _ptr(keys_b), _ptr(vals_b), M, end_bit,
-                                  _ptr(scratch), scratch.numel(), C.byref(in_b), st), "b200_sort_pairs",
-              kernels=(2 + (end_bit + 7) // 8) if M > 0 else 0)
-    keys_s, vals_s = (keys_b, vals_b) if in_b.value else (keys_a, vals_a)
-    offsets = torch.empty(n_tiles, dtype=torch.int32, device=dev)
+        check(lib.b200_sort_pairs_k16(_ptr(tkeys_a), _ptr(vals_a), _ptr(tkeys_b), _ptr(vals_b), M, tbits,
+                                      _ptr(scratch_m), scratch_m.numel(), C.byref(in_b), st), "b200_sort_pairs_k16",
+              kernels=(2 + (tbits + 7) // 8) if M > 0 else 0)
+    tkeys_s, vals_s = (tkeys_b, vals_b) if in_b.value else (tkeys_a, vals_a)
     with _stage("tile_ranges"):
-        check(lib.b200_tile_ranges(_ptr(keys_s), M, n_tiles, _ptr(offsets), st), "b200_tile_ranges")
-    out.update(isect_ids=keys_s[:M], flatten_ids=vals_s[:M], isect_offsets=offsets.view(tile_h, tile_w))
+        check(lib.b200_tile_ranges_k16(_ptr(tkeys_s), M, n_tiles, _ptr(offsets), st), "b200_tile_ranges_k16",
+              kernels=1 if M > 0 else 0)
+    out.update(M=M, flatten_ids=vals_s[:M], isect_offsets=offsets.view(tile_h, tile_w), tile_keys=tkeys_s[:M])
+    if with_isect_ids:
+        ids = torch.empty(max(M, 1), dtype=torch.int64, device=dev)
+        check(lib.b200_isect_ids(_ptr(tkeys_s), _ptr(vals_s), _ptr(splats), M, _ptr(ids), st), "b200_isect_ids",
+              kernels=1 if M > 0 else 0)
+        out["isect_ids"] = ids[:M]
+    else:
+        out["isect_ids"] = None
     return out
 
 
@@ -136,13 +198,17 @@ class RasterizeSplats(torch.autograd.Function):
 
     @staticmethod
     @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
-    def forward(ctx, means, quats, scales, opacities, colors, cam, width, height, sh_degree, chset, background):
+    def forward(ctx, means, quats, scales, opacities, colors, cam, width, height, sh_degree, chset, background,
+                with_isect_ids=False, method="auto"):
         _require_cuda(means, quats, scales, opacities, colors)
         means, quats, scales = means.contiguous(), quats.contiguous(), scales.contiguous()
         opacities, colors = opacities.contiguous(), colors.contiguous()
         dev = means.device
         with torch.cuda.device(dev):
-            b = project_and_bin(means, quats, scales, opacities, colors, sh_degree, cam, width, height)
+            b = project_and_bin(means, quats, scales, opacities, colors, sh_degree, cam, width, height,
+                                method=method, with_isect_ids=with_isect_ids)
+            if b["isect_ids"] is None:
+                b["isect_ids"] = torch.empty(0, dtype=torch.int64, device=dev)
             nch = _NCH[chset]
             render = torch.empty(height, width, nch, dtype=torch.float32, device=dev)
             alpha = torch.empty(height, width, 1, dtype=torch.float32, device=dev)
@@ -194,11 +260,11 @@ class RasterizeSplats(torch.autograd.Function):
                                               sh_coeffs, deg, N, cam, width, height, _ptr(radii), _ptr(v_splats),
                                               _ptr(v_means), _ptr(v_quats), _ptr(v_scales), _ptr(v_opac),
                                               _ptr(v_colors), st), "b200_project_sh_bwd")
-        return v_means, v_quats, v_scales, v_opac, v_colors, None, None, None, None, None, None
+        return v_means, v_quats, v_scales, v_opac, v_colors, None, None, None, None, None, None, None, None
 
 
 def _render_one(means, quats, scales, opacities, colors, viewmat, K, width, height, sh_degree, render_mode,
-                background, near_plane, far_plane, eps2d, radius_clip):
+                background, near_plane, far_plane, eps2d, radius_clip, with_isect_ids=False, method="auto"):
     chset = _MODES[render_mode]
     nch = _NCH[chset]
     if background is None:
@@ -213,7 +279,7 @@ def _render_one(means, quats, scales, opacities, colors, viewmat, K, width, heig
             bg = bgl[:3] + [0.0]  # depth channel composites over 0
     cam = make_cam(viewmat, K, near_plane, far_plane, eps2d, radius_clip)
     out = RasterizeSplats.apply(means, quats, scales, opacities, colors, cam, int(width), int(height), sh_degree,
-                                chset, bg)
+                                chset, bg, with_isect_ids, method)
     render, alpha, radii, splats, tiles_per_gauss, isect_ids, flatten_ids, offsets, last_ids = out
     if render_mode in ("ED", "RGB+ED"):
         render = torch.cat([render[..., :-1], render[..., -1:] / alpha.clamp(min=1e-10)], dim=-1)
@@ -226,12 +292,16 @@ def rasterization(means: torch.Tensor, quats: torch.Tensor, scales: torch.Tensor
                   near_plane: float = 0.01, far_plane: float = 1e10, radius_clip: float = 0.0,
                   eps2d: float = 0.3, sh_degree: Optional[int] = None, packed: bool = False,
                   tile_size: int = 16, backgrounds: Optional[torch.Tensor] = None, render_mode: str = "RGB",
-                  **unsupported) -> Tuple[torch.Tensor, torch.Tensor, Dict]:
+                  meta_isect_ids: bool = False, binning: str = "auto", **unsupported) -> Tuple[torch.Tensor, torch.Tensor, Dict]:
     """Drop-in for ``gsplat.rasterization`` with the argument set the reference uses.
 
     means[N,3] quats[N,4](wxyz) scales[N,3] opacities[N] colors=[N,K,3] SH coefficients (``sh_degree``
     given) or [N,3] colours; viewmats[C,4,4] world->camera, Ks[C,3,3] pixel intrinsics.  Returns
     ``(renders[C,H,W,CH], alphas[C,H,W,1], meta)``.
+
+    Extensions (not gsplat arguments): ``meta_isect_ids=True`` materialises the sorted int64
+    ``meta["isect_ids"]`` (the fast path never needs them: the reference reads only ``means2d`` and
+    ``radii``, gsplat_backend.py:204-208); ``binning`` selects "split" / "keys64" / "auto" (project_and_bin).
     """
     if render_mode not in _MODES:
         raise ValueError(f"render_mode must be one of {sorted(_MODES)}, got {render_mode!r}")
@@ -252,7 +322,7 @@ def rasterization(means: torch.Tensor, quats: torch.Tensor, scales: torch.Tensor
     for c in range(Ccam):
         bg = None if backgrounds is None else (backgrounds[c] if backgrounds.dim() == 2 else backgrounds)
         r, a, m = _render_one(means, quats, scales, opacities, colors, viewmats[c], Ks[c], width, height, sh_degree,
-                              render_mode, bg, near_plane, far_plane, eps2d, radius_clip)
+                              render_mode, bg, near_plane, far_plane, eps2d, radius_clip, meta_isect_ids, binning)
         renders.append(r)
         alphas.append(a)
         metas.append(m)

@@ -63,13 +63,15 @@ const char* b200_last_error(void);
  *   means[N,3] quats[N,4] scales[N,3] (post-exp) opacities[N] (post-sigmoid) shs[N,sh_coeffs,3]
  *   sh_degree in 0..3 with (sh_degree+1)^2 <= sh_coeffs; sh_degree < 0 => `shs` is [N,3] plain colours.
  * Outputs: radii[N,2] int32, splats[N,12], tiles_per_gauss[N] int32,
- *          block_sums[b200_project_blocks(N)] int64 (sum of tiles_per_gauss per 256-Gaussian block). */
+ *          block_sums[b200_project_blocks(N)] int64 (sum of tiles_per_gauss per 256-Gaussian block);
+ *          optional (both or neither NULL) depth_keys[N] uint32 = fp32 depth bits (0xFFFFFFFF if culled)
+ *          and gauss_ids[N] = 0..N-1, the input of the split-key sort below. */
 int64_t b200_project_blocks(int64_t N);
 int b200_project_sh_fwd(const float* means, const float* quats, const float* scales,
                         const float* opacities, const float* shs, int sh_coeffs, int sh_degree,
                         int64_t N, const float* cam_host, int width, int height,
                         int32_t* radii, float* splats, int32_t* tiles_per_gauss,
-                        int64_t* block_sums, void* stream);
+                        int64_t* block_sums, uint32_t* depth_keys, int32_t* gauss_ids, void* stream);
 
 /* ---- stage 2a: exclusive scan of block sums; writes block_offsets[nblocks] and total[1] -------
  * (the cumsum half of gsplat isect_tiles).  Single CTA; nblocks = b200_project_blocks(N). */
@@ -92,6 +94,31 @@ size_t b200_sort_scratch_bytes(int64_t M);
 int b200_sort_pairs(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b,
                     int64_t M, int end_bit, void* scratch, size_t scratch_bytes,
                     int* result_in_b_host, void* stream);
+
+int b200_sort_pairs_k32(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b,
+                        int64_t M, int end_bit, void* scratch, size_t scratch_bytes,
+                        int* result_in_b_host, void* stream);
+int b200_sort_pairs_k16(uint16_t* keys_a, uint32_t* vals_a, uint16_t* keys_b, uint32_t* vals_b,
+                        int64_t M, int end_bit, void* scratch, size_t scratch_bytes,
+                        int* result_in_b_host, void* stream);
+
+/* ---- stage 2b'/2c': split-key form of the same sort (the fast path) ----------------------------
+ * An LSD radix sort of (tile<<32 | depth) keys visits the depth digits first and the tile digits
+ * last.  Depth digits do not depend on the tile, so they are sorted over the N Gaussians BEFORE the
+ * duplication (b200_sort_pairs_k32 on depth_keys/gauss_ids -> perm), the duplicates are emitted in
+ * that order with 16-bit tile keys, and only the tile digits are sorted over the M intersections
+ * (b200_sort_pairs_k16).  Output order is identical to sorting the 64-bit keys (ties: ascending
+ * Gaussian index); b200_isect_ids rebuilds the sorted 64-bit keys when a caller wants them.
+ * Requires tile_w*tile_h <= 65536. */
+int b200_bin_count_sorted(const int32_t* tiles_per_gauss, const int32_t* perm, int64_t N,
+                          int64_t* block_sums, void* stream);
+int b200_bin_emit_sorted(const float* splats, const int32_t* radii, const int32_t* tiles_per_gauss,
+                         const int32_t* perm, const int64_t* block_offsets, int64_t N, int width,
+                         int height, int64_t M, uint16_t* tile_keys, int32_t* flatten_ids, void* stream);
+int b200_tile_ranges_k16(const uint16_t* sorted_tile_keys, int64_t M, int n_tiles, int32_t* offsets,
+                         void* stream);
+int b200_isect_ids(const uint16_t* sorted_tile_keys, const int32_t* flatten_ids, const float* splats,
+                   int64_t M, int64_t* isect_ids, void* stream);
 
 /* ---- stage 2d: per-tile ranges (gsplat isect_offset_encode) ---------------------------------
  * offsets[n_tiles] int32 = first sorted index whose tile id >= t; all M's for trailing empty tiles. */

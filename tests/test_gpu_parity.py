@@ -45,7 +45,7 @@ def _gpu_full(pkg, act, sc, W, H, deg, mode="RGB", bg=None, requires_grad=False)
     r, al, meta = pkg.rasterization(
         leaves["means3D"], leaves["rotations"], leaves["scales"], leaves["opacities"], leaves["shs"],
         sc["viewmat"].to(DEV)[None], sc["K"].to(DEV)[None], W, H, sh_degree=deg, render_mode=mode,
-        backgrounds=None if bg is None else bg.to(DEV)[None])
+        backgrounds=None if bg is None else bg.to(DEV)[None], meta_isect_ids=True)
     return r[0], al[0], meta, leaves
 
 
@@ -97,13 +97,51 @@ def test_culling_cases(pkg, oracle):
 # ------------------------------------------------------------------------------------------------
 # stage 2: binning / sort / ranges — bit exact
 # ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("N,W,H", [(3000, 160, 96), (50000, 640, 360), (20000, 1920, 1080), (30000, 3840, 2160)])
+def test_split_key_binning_bit_exact(pkg, oracle, N, W, H):
+    """Fast path (depth digits sorted over Gaussians, 16-bit tile digits over intersections) must give the
+    same sorted keys / ids / ranges as a stable sort of the 64-bit keys."""
+    sc, act = _scene(oracle, N, W, H, seed=3)
+    a = _cuda(act)
+    cam = pkg.make_cam(sc["viewmat"], sc["K"])
+    b = pkg.project_and_bin(a["means3D"], a["rotations"], a["scales"], a["opacities"].squeeze(-1).contiguous(),
+                            a["shs"], 3, cam, W, H, method="split", with_isect_ids=True)
+    sp, radii = b["splats"].cpu(), b["radii"].cpu()
+    ob = oracle.bin_tiles(sp[:, 0:2], radii, sp[:, 9], W, H)
+    assert b["M"] == int(ob["cum_tiles"][-1])
+    ids_s, flat_s, offs = oracle.sort_and_ranges(ob["isect_ids"], ob["flatten_ids"], ob["tile_w"], ob["tile_h"])
+    assert torch.equal(b["isect_ids"].cpu(), ids_s)
+    assert torch.equal(b["flatten_ids"].cpu(), flat_s)
+    assert torch.equal(b["isect_offsets"].cpu(), offs)
+    # and the literal 64-bit path agrees with it
+    b64 = pkg.project_and_bin(a["means3D"], a["rotations"], a["scales"], a["opacities"].squeeze(-1).contiguous(),
+                              a["shs"], 3, cam, W, H, method="keys64")
+    assert torch.equal(b64["flatten_ids"], b["flatten_ids"]) and torch.equal(b64["isect_ids"], b["isect_ids"])
+    assert torch.equal(b64["isect_offsets"], b["isect_offsets"])
+
+
+def test_split_key_ties_keep_gaussian_order(pkg, oracle):
+    """Many Gaussians at identical depth in the same tiles: ties must resolve by ascending Gaussian index."""
+    N, W, H = 5000, 128, 96
+    sc, act = _scene(oracle, N, W, H, seed=13)
+    act["means3D"][:, 2] = torch.tensor([3.0, 5.0, 7.0])[torch.arange(N) % 3]
+    a = _cuda(act)
+    cam = pkg.make_cam(sc["viewmat"], sc["K"])
+    b = pkg.project_and_bin(a["means3D"], a["rotations"], a["scales"], a["opacities"].squeeze(-1).contiguous(),
+                            a["shs"], 3, cam, W, H, method="split", with_isect_ids=True)
+    sp, radii = b["splats"].cpu(), b["radii"].cpu()
+    ob = oracle.bin_tiles(sp[:, 0:2], radii, sp[:, 9], W, H)
+    ids_s, flat_s, offs = oracle.sort_and_ranges(ob["isect_ids"], ob["flatten_ids"], ob["tile_w"], ob["tile_h"])
+    assert torch.equal(b["flatten_ids"].cpu(), flat_s) and torch.equal(b["isect_ids"].cpu(), ids_s)
+
+
 @pytest.mark.parametrize("N,W,H", [(3000, 160, 96), (50000, 640, 360), (20000, 1920, 1080)])
 def test_binning_sort_ranges_bit_exact(pkg, oracle, N, W, H):
     sc, act = _scene(oracle, N, W, H, seed=3)
     a = _cuda(act)
     cam = pkg.make_cam(sc["viewmat"], sc["K"])
     b = pkg.project_and_bin(a["means3D"], a["rotations"], a["scales"], a["opacities"].squeeze(-1).contiguous(),
-                            a["shs"], 3, cam, W, H, keep_unsorted=True)
+                            a["shs"], 3, cam, W, H, keep_unsorted=True, method="keys64")
     sp = b["splats"].cpu()
     radii = b["radii"].cpu()
     # binning oracle on the GPU's own projection outputs ("bit-exact given identical inputs", SURVEY §7.3-2)
@@ -170,6 +208,38 @@ def test_radix_sort_pairs_stable(pkg, n, end_bit):
     ks, vs = (kb, vb) if in_b.value else (ka, va)
     order = torch.sort(keys, stable=True).indices
     assert torch.equal(ks[:n].cpu(), keys[order])
+    assert torch.equal(vs[:n].cpu(), vals[order])
+
+
+@pytest.mark.parametrize("n", [0, 1, 4097, 250_001, 2_000_000])
+@pytest.mark.parametrize("width,end_bit", [(16, 13), (16, 15), (16, 16), (32, 32), (32, 20)])
+def test_radix_sort_narrow_keys_stable(pkg, n, width, end_bit):
+    """16-bit (tile) and 32-bit (depth) key variants used by the split-key path."""
+    lib, L = pkg._lib.lib, pkg._lib
+    g = torch.Generator().manual_seed(n * 7 + end_bit)
+    keys = torch.randint(0, 2 ** end_bit, (max(n, 1),), generator=g, dtype=torch.int64)[:n]
+    if n > 10:
+        keys[: n // 3] &= 0x3F
+    vals = torch.arange(n, dtype=torch.int32)
+    kdt = torch.int16 if width == 16 else torch.int32
+    wrap = keys.clone()
+    half = 1 << (width - 1)
+    wrap[wrap >= half] -= (1 << width)  # two's-complement storage of the unsigned key
+    ka, va = wrap.to(kdt).to(DEV), vals.to(DEV)
+    if n == 0:
+        ka, va = torch.empty(1, dtype=kdt, device=DEV), torch.empty(1, dtype=torch.int32, device=DEV)
+    kb, vb = torch.empty_like(ka), torch.empty_like(va)
+    sb = lib.b200_sort_scratch_bytes(n)
+    scratch = torch.empty(sb, dtype=torch.uint8, device=DEV)
+    in_b = C.c_int(0)
+    fn = lib.b200_sort_pairs_k16 if width == 16 else lib.b200_sort_pairs_k32
+    L.check(fn(ka.data_ptr(), va.data_ptr(), kb.data_ptr(), vb.data_ptr(), n, end_bit, scratch.data_ptr(), sb,
+               C.byref(in_b), None), "sort")
+    torch.cuda.synchronize()
+    ks, vs = (kb, vb) if in_b.value else (ka, va)
+    order = torch.sort(keys, stable=True).indices
+    got = ks[:n].cpu().to(torch.int64) & ((1 << width) - 1)
+    assert torch.equal(got, keys[order])
     assert torch.equal(vs[:n].cpu(), vals[order])
 
 
