@@ -26,6 +26,20 @@
 
 namespace {
 
+// Lanes of `act` holding the same 8-bit digit.  Eight ballots pipeline back to back, whereas MATCH.ANY
+// serialises on the number of distinct values in the warp (measured: short-scoreboard stalls dominated
+// the first version of the ranking loop, profiles/ncu_r01_summary.md).
+__device__ __forceinline__ unsigned digit_peers(unsigned act, uint32_t d) {
+    unsigned peers = act;
+#pragma unroll
+    for (int b = 0; b < RS_BITS; ++b) {
+        const bool bit = (d >> b) & 1u;
+        const unsigned vote = __ballot_sync(act, bit);
+        peers &= bit ? vote : ~vote;
+    }
+    return peers;
+}
+
 // All per-pass digit histograms in one read of the keys.
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
@@ -45,7 +59,7 @@ rs_hist_kernel(const KeyT* __restrict__ keys, int64_t n, int npasses, int end_bi
                 int shift = p * RS_BITS;
                 int bits = min(RS_BITS, end_bit - shift);
                 uint32_t d = (uint32_t)(k >> shift) & ((1u << bits) - 1u);
-                unsigned peers = __match_any_sync(act, d);
+                unsigned peers = digit_peers(act, d);
                 if ((__ffs(peers) - 1) == lane) atomicAdd(&s_hist[p * RS_RADIX + d], __popc(peers));
             }
         }
@@ -117,20 +131,19 @@ rs_onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict_
         val[i] = ok ? vals_in[tile_base + local] : 0u;
     }
     // ---- rank inside the warp by digit, in order ----
+    // One shared-memory atomic per (item, distinct digit), issued by the group's lowest lane; a warp's
+    // shared-memory operations execute in issue order, so successive items need no barrier and the 16
+    // ballot/atomic/shuffle chains overlap.
     const unsigned lt_mask = (1u << lane) - 1u;
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; ++i) {
         uint32_t d = (uint32_t)((uint64_t)key[i] >> shift) & dmask;
-        unsigned peers = __match_any_sync(0xffffffffu, d);
+        unsigned peers = digit_peers(0xffffffffu, d);
         int leader = __ffs(peers) - 1;
         uint32_t base = 0;
-        if (lane == leader) {
-            base = S.warp_hist[wid][d];
-            S.warp_hist[wid][d] = base + __popc(peers);
-        }
+        if (lane == leader) base = atomicAdd(&S.warp_hist[wid][d], (uint32_t)__popc(peers));
         base = __shfl_sync(0xffffffffu, base, leader);
         pos[i] = base + __popc(peers & lt_mask);
-        __syncwarp();
     }
     __syncthreads();
     // ---- per digit (thread d): exclusive prefix over warps, tile count ----
