@@ -1,0 +1,69 @@
+"""world_size-2 gloo test (CPU) of the view-sharding + flat gradient all-reduce host logic:
+the reduced gradient must equal the single-process gradient of the MEAN loss over the same views
+(reference semantics: src/training/trainer.py:458-500)."""
+import importlib
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _loss(params, view):
+    a, b = params
+    return ((a * view["w"]).sum() + (b ** 2 * view["s"]).sum()) * view["k"]
+
+
+def _views(n):
+    g = torch.Generator().manual_seed(0)
+    return [{"w": torch.randn(7, 3, generator=g), "s": torch.randn(5, generator=g), "k": float(i + 1)} for i in range(n)]
+
+
+def _worker(rank, world, port, n_views, out):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    pkg = importlib.import_module("3d-gaussian-splatting_b200")
+    torch.manual_seed(1)
+    params = [torch.randn(7, 3, requires_grad=True), torch.randn(5, requires_grad=True)]
+    views = _views(n_views)
+    assert pkg.shard_views(n_views, rank, world) == list(range(rank, n_views, world))
+    step = pkg.ViewShardedStep(params)
+    mean_loss = step(views, lambda v: _loss(params, v))
+    out[rank] = (mean_loss, [p.grad.clone() for p in params])
+    dist.destroy_process_group()
+
+
+def test_view_sharded_gradients_equal_single_process_mean(tmp_path):
+    world, n_views = 2, 5  # uneven shard: rank 0 gets 3 views, rank 1 gets 2
+    port = 29500 + (os.getpid() % 500)
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(world, port, n_views, out), nprocs=world, join=True)
+    torch.manual_seed(1)
+    params = [torch.randn(7, 3, requires_grad=True), torch.randn(5, requires_grad=True)]
+    views = _views(n_views)
+    loss = sum(_loss(params, v) for v in views) / n_views
+    loss.backward()
+    for r in range(world):
+        ml, grads = out[r]
+        assert abs(ml - float(loss)) < 1e-5 * max(1.0, abs(float(loss)))
+        for g, p in zip(grads, params):
+            torch.testing.assert_close(g, p.grad, rtol=1e-5, atol=1e-6)
+    # replicas identical
+    for g0, g1 in zip(out[0][1], out[1][1]):
+        assert torch.equal(g0, g1)
+
+
+def test_shard_views_partition():
+    sys.path.insert(0, ROOT)
+    pkg = importlib.import_module("3d-gaussian-splatting_b200")
+    for n in (0, 1, 7, 64):
+        for w in (1, 2, 4, 8):
+            allv = sorted(i for r in range(w) for i in pkg.shard_views(n, r, w))
+            assert allv == list(range(n))
+            sizes = [len(pkg.shard_views(n, r, w)) for r in range(w)]
+            assert max(sizes) - min(sizes) <= 1
