@@ -238,7 +238,7 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
 }
 
 template <int DEG>
-__global__ void __launch_bounds__(PROJ_THREADS)
+__global__ void __launch_bounds__(PROJ_THREADS, 2)
 project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__ quats,
                       const float* __restrict__ scales, const float* __restrict__ opacities,
                       const float* __restrict__ shs, int sh_coeffs, bool vec_ok, int64_t N, Cam cam,
@@ -296,19 +296,25 @@ project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__
             float vr[3];
 #pragma unroll
             for (int ch = 0; ch < 3; ++ch) vr[ch] = (rgb[ch] + 0.5f >= 0.f) ? v_col[ch] : 0.f;
-            // coefficient gradients
-            float out[48];
-#pragma unroll
-            for (int k = 0; k < 16; ++k) {
-#pragma unroll
-                for (int ch = 0; ch < 3; ++ch) out[3 * k + ch] = (k < NB) ? B[k] * vr[ch] : 0.f;
-            }
+            // coefficient gradients: v_c[k][ch] = B_k * v_rgb[ch], zero above the active degree
             if (vec_ok && sh_coeffs == 16) {
 #pragma unroll
-                for (int i = 0; i < 12; ++i)
-                    reinterpret_cast<float4*>(vsh)[i] = make_float4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]);
+                for (int i = 0; i < 12; ++i) {
+                    float o4[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        constexpr int dummy = 0; (void)dummy;
+                        const int e = 4 * i + j, k = e / 3, ch = e - 3 * k;
+                        o4[j] = (k < NB) ? B[k < NB ? k : 0] * vr[ch] : 0.f;
+                    }
+                    reinterpret_cast<float4*>(vsh)[i] = make_float4(o4[0], o4[1], o4[2], o4[3]);
+                }
             } else {
-                for (int i = 0; i < ncoef_f; ++i) vsh[i] = (i < 48) ? out[i] : 0.f;
+#pragma unroll
+                for (int k = 0; k < NB; ++k) {
+                    vsh[3 * k] = B[k] * vr[0]; vsh[3 * k + 1] = B[k] * vr[1]; vsh[3 * k + 2] = B[k] * vr[2];
+                }
+                for (int i = 3 * NB; i < ncoef_f; ++i) vsh[i] = 0.f;
             }
             // direction gradient
             float gk[NB];

@@ -8,6 +8,7 @@
 // formulation, and the split form the fast path uses — 32-bit depth keys over Gaussians BEFORE tile
 // duplication followed by 16-bit tile keys over intersections (the same LSD digit order, with the
 // duplication moved between the depth digits and the tile digits; see DESIGN.md "Sort").
+#include <stdlib.h>
 #include "common.cuh"
 
 #define RS_BITS 8
@@ -40,33 +41,57 @@ __device__ __forceinline__ unsigned digit_peers(unsigned act, uint32_t d) {
     return peers;
 }
 
-// All per-pass digit histograms in one read of the keys.
+// All per-pass digit histograms in one read of the keys.  Each warp owns private histogram rows in
+// shared memory and updates them with plain LDS/STS from the lowest lane of every digit group: shared
+// ATOMICS cost ~2 cycles per distinct address (B300_MICROARCH.md) and with high-entropy digits that is
+// 60 cycles per warp instruction — it, not HBM, bounded the first two versions (60 us for a 13 MB read).
+// Block size is chosen by the launcher so that warps * npasses <= 32 rows (32 KB).
+#define RS_HIST_ROWS 32
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
 rs_hist_kernel(const KeyT* __restrict__ keys, int64_t n, int npasses, int end_bit, uint32_t* __restrict__ hist) {
-    __shared__ uint32_t s_hist[RS_MAX_PASSES * RS_RADIX];
-    for (int i = threadIdx.x; i < npasses * RS_RADIX; i += blockDim.x) s_hist[i] = 0;
+    constexpr int VEC = 16 / sizeof(KeyT);
+    __shared__ uint32_t s_hist[RS_HIST_ROWS * RS_RADIX];
+    const int nwarps = blockDim.x >> 5;
+    for (int i = threadIdx.x; i < nwarps * npasses * RS_RADIX; i += blockDim.x) s_hist[i] = 0;
     __syncthreads();
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t* my_rows = s_hist + wid * npasses * RS_RADIX;
+    const int64_t nchunks = (n + VEC - 1) / VEC;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    const int64_t n_round = (n + 31) / 32 * 32;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
-        const bool valid = i < n;
-        const uint64_t k = valid ? (uint64_t)keys[i] : 0;
-        const unsigned act = __ballot_sync(0xffffffffu, valid);
-        if (valid) {
+    const int iters = (int)((nchunks + stride - 1) / stride);  // block-uniform trip count: ballots stay plain VOTEs
+    const bool aligned = ((uintptr_t)keys & 15) == 0;
+    for (int it = 0; it < iters; ++it) {
+        const int64_t c = ((int64_t)it * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+        KeyT k[VEC];
+        const int64_t base = c * VEC;
+        if (aligned && base + VEC <= n) {
+            const uint4 raw = __ldg(reinterpret_cast<const uint4*>(keys) + c);
+            memcpy(k, &raw, 16);
+        } else {
+#pragma unroll
+            for (int v = 0; v < VEC; ++v) k[v] = (base + v < n) ? keys[base + v] : (KeyT)0;
+        }
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) {
+            const bool valid = base + v < n;
+            const unsigned vmask = __ballot_sync(0xffffffffu, valid);
             for (int p = 0; p < npasses; ++p) {
-                int shift = p * RS_BITS;
-                int bits = min(RS_BITS, end_bit - shift);
-                uint32_t d = (uint32_t)(k >> shift) & ((1u << bits) - 1u);
-                unsigned peers = digit_peers(act, d);
-                if ((__ffs(peers) - 1) == lane) atomicAdd(&s_hist[p * RS_RADIX + d], __popc(peers));
+                const int shift = p * RS_BITS;
+                const int bits = min(RS_BITS, end_bit - shift);
+                const uint32_t d = (uint32_t)((uint64_t)k[v] >> shift) & ((1u << bits) - 1u);
+                const unsigned peers = digit_peers(0xffffffffu, d) & vmask;
+                if (valid && (__ffs(peers) - 1) == lane) my_rows[p * RS_RADIX + d] += __popc(peers);
+                __syncwarp();
             }
         }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < npasses * RS_RADIX; i += blockDim.x)
-        if (s_hist[i]) atomicAdd(&hist[i], s_hist[i]);
+    for (int i = threadIdx.x; i < npasses * RS_RADIX; i += blockDim.x) {
+        uint32_t tot = 0;
+        for (int w = 0; w < nwarps; ++w) tot += s_hist[w * npasses * RS_RADIX + i];
+        if (tot) atomicAdd(&hist[i], tot);
+    }
 }
 
 // Exclusive scan of each pass's 256 bins, in place.
@@ -100,7 +125,7 @@ struct __align__(16) RsSmem {
     uint32_t tile;
 };
 
-template <typename KeyT>
+template <typename KeyT, bool USE_MATCH>
 __global__ void __launch_bounds__(RS_THREADS)
 rs_onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                    KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n, int shift, int bits,
@@ -131,19 +156,23 @@ rs_onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict_
         val[i] = ok ? vals_in[tile_base + local] : 0u;
     }
     // ---- rank inside the warp by digit, in order ----
-    // One shared-memory atomic per (item, distinct digit), issued by the group's lowest lane; a warp's
-    // shared-memory operations execute in issue order, so successive items need no barrier and the 16
-    // ballot/atomic/shuffle chains overlap.
+    // The warp's histogram row is private to it, so the lowest lane of each digit group updates it
+    // with a plain load + store (no shared atomics: ~2 cycles per distinct address, i.e. up to 60 cycles
+    // per item for high-entropy digits); __syncwarp orders the row between successive items.
     const unsigned lt_mask = (1u << lane) - 1u;
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; ++i) {
         uint32_t d = (uint32_t)((uint64_t)key[i] >> shift) & dmask;
-        unsigned peers = digit_peers(0xffffffffu, d);
+        unsigned peers = USE_MATCH ? __match_any_sync(0xffffffffu, d) : digit_peers(0xffffffffu, d);
         int leader = __ffs(peers) - 1;
         uint32_t base = 0;
-        if (lane == leader) base = atomicAdd(&S.warp_hist[wid][d], (uint32_t)__popc(peers));
+        if (lane == leader) {
+            base = S.warp_hist[wid][d];
+            S.warp_hist[wid][d] = base + __popc(peers);
+        }
         base = __shfl_sync(0xffffffffu, base, leader);
         pos[i] = base + __popc(peers & lt_mask);
+        __syncwarp();
     }
     __syncthreads();
     // ---- per digit (thread d): exclusive prefix over warps, tile count ----
@@ -251,7 +280,8 @@ int sort_pairs_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_t* vals
     cudaStream_t st = (cudaStream_t)stream;
     static bool attr_set = false;  // one flag per template instantiation
     if (!attr_set) {
-        cudaFuncSetAttribute(rs_onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem<KeyT>));
+        cudaFuncSetAttribute(rs_onesweep_kernel<KeyT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem<KeyT>) + 160 * 1024);
+        cudaFuncSetAttribute(rs_onesweep_kernel<KeyT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem<KeyT>) + 160 * 1024);
         attr_set = true;
     }
     const size_t ntiles = (size_t)((M + RS_TILE - 1) / RS_TILE);
@@ -260,15 +290,26 @@ int sort_pairs_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_t* vals
     uint32_t* status = tickets + 64;
     const size_t used = (RS_MAX_PASSES * RS_RADIX + 64) * sizeof(uint32_t) + (size_t)npasses * ntiles * RS_RADIX * sizeof(uint32_t);
     cudaMemsetAsync(scratch, 0, used, st);
-    int hist_blocks = (int)min((int64_t)148 * 8, (M + 255) / 256);
-    rs_hist_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_a, M, npasses, end_bit, hist);
+    static int pad = -1;
+    if (pad < 0) { const char* e = getenv("B200_SORT_SMEM_PAD"); pad = e ? atoi(e) : 0; }
+    static int use_match = -1;
+    if (use_match < 0) { const char* e = getenv("B200_SORT_MATCH"); use_match = (e && e[0] == '1') ? 1 : 0; }
+    static int hb = -1;
+    if (hb < 0) { const char* e = getenv("B200_HIST_BLOCKS"); hb = e ? atoi(e) : 148 * 2; }
+    int hist_blocks = (int)min((int64_t)hb, (M + 255) / 256);
+    const int hist_threads = (npasses <= 4) ? 256 : 128;  // warps * npasses <= RS_HIST_ROWS
+    rs_hist_kernel<KeyT><<<hist_blocks, hist_threads, 0, st>>>(keys_a, M, npasses, end_bit, hist);
     rs_scan_kernel<<<npasses, RS_RADIX, 0, st>>>(hist);
     KeyT* kin = keys_a; uint32_t* vin = vals_a; KeyT* kout = keys_b; uint32_t* vout = vals_b;
     for (int p = 0; p < npasses; ++p) {
         int shift = p * RS_BITS;
         int bits = (end_bit - shift) < RS_BITS ? (end_bit - shift) : RS_BITS;
-        rs_onesweep_kernel<KeyT><<<(unsigned)ntiles, RS_THREADS, sizeof(RsSmem<KeyT>), st>>>(
-            kin, vin, kout, vout, M, shift, bits, hist + p * RS_RADIX, status + (size_t)p * ntiles * RS_RADIX, tickets + p);
+        if (use_match)
+            rs_onesweep_kernel<KeyT, true><<<(unsigned)ntiles, RS_THREADS, sizeof(RsSmem<KeyT>) + pad, st>>>(
+                kin, vin, kout, vout, M, shift, bits, hist + p * RS_RADIX, status + (size_t)p * ntiles * RS_RADIX, tickets + p);
+        else
+            rs_onesweep_kernel<KeyT, false><<<(unsigned)ntiles, RS_THREADS, sizeof(RsSmem<KeyT>) + pad, st>>>(
+                kin, vin, kout, vout, M, shift, bits, hist + p * RS_RADIX, status + (size_t)p * ntiles * RS_RADIX, tickets + p);
         KeyT* tk = kin; kin = kout; kout = tk;
         uint32_t* tv = vin; vin = vout; vout = tv;
     }

@@ -4,11 +4,12 @@
 // Gaussian's ten partial sums over its four pixels in registers, the warp reduces them once per
 // (Gaussian, half tile) with shuffles, and lane 0 issues three 16-byte vector REDs into the 48-B
 // gradient record — 3 L2 atomic operations per (Gaussian, half tile) instead of 10 per warp of 32 px.
+#include <stdlib.h>
 #include "raster_common.cuh"
 
 namespace {
 
-template <int CHSET>
+template <int CHSET, bool BFLY>
 __global__ void __launch_bounds__(RU_THREADS)
 raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__ flatten_ids,
                   const int32_t* __restrict__ offsets, int M, int W, int H, int tile_w, int n_tiles, Bg bg,
@@ -138,22 +139,43 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
                     }
                 }
             }
+            if (BFLY) {
+            // one transposing reduction for eight sums, plain trees for the one or two that remain; then a
+                // single RED instruction: lane 4k adds total k to record slot k, lanes 1/2 add the extras.
+                float v8[8] = {Sx, Sy, Sxx, Sxy, Syy, g_o, HAS_RGB ? g_col[0] : 0.f, HAS_RGB ? g_col[1] : 0.f};
+                float tot = warp_reduce8_transposed(v8, lane);
+                float ex0 = 0.f, ex1 = 0.f;
+                if (HAS_RGB) ex0 = warp_sum(g_col[2]);
+                if (HAS_D) ex1 = warp_sum(g_col[CH - 1]);
+                const float other = __shfl_xor_sync(0xffffffffu, tot, 4);  // Sy for the Sx lanes and vice versa
+                const int k = lane >> 2;
+                float val = tot;
+                if (k == 0) val = a.z * tot + a.w * other;        // v_mx = A Sx + B Sy
+                else if (k == 1) val = b.x * tot + a.w * other;   // v_my = C Sy + B Sx
+                else if (k == 2 || k == 4) val = 0.5f * tot;      // v_A = Sxx / 2, v_C = Syy / 2
+                int slot = (lane & 3) == 0 ? k : -1;
+                if (!HAS_RGB && k >= 6) slot = -1;
+                if (lane == 1 && HAS_RGB) { slot = 8; val = ex0; }
+                if (lane == 2 && HAS_D) { slot = 9; val = ex1; }
+                if (slot >= 0) atomicAdd(v_splats + (size_t)stage[j].id * SPLAT_F + slot, val);
+            } else {
 #pragma unroll
-            for (int c = 0; c < CH; ++c) g_col[c] = warp_sum(g_col[c]);
-            g_o = warp_sum(g_o);
-            Sx = warp_sum(Sx); Sy = warp_sum(Sy);
-            Sxx = warp_sum(Sxx); Sxy = warp_sum(Sxy); Syy = warp_sum(Syy);
-            if (lane == 0) {
-                float* out = v_splats + (size_t)stage[j].id * SPLAT_F;
-                const float v_mx = a.z * Sx + a.w * Sy, v_my = a.w * Sx + b.x * Sy;
-                red_add_v4(out, v_mx, v_my, 0.5f * Sxx, Sxy);
-                if (HAS_RGB) {
-                    red_add_v4(out + 4, 0.5f * Syy, g_o, g_col[0], g_col[1]);
-                    if (HAS_D) red_add_v2(out + 8, g_col[2], g_col[3]);
-                    else atomicAdd(out + 8, g_col[2]);
-                } else {
-                    red_add_v2(out + 4, 0.5f * Syy, g_o);
-                    atomicAdd(out + 9, g_col[0]);
+                for (int c = 0; c < CH; ++c) g_col[c] = warp_sum(g_col[c]);
+                g_o = warp_sum(g_o);
+                Sx = warp_sum(Sx); Sy = warp_sum(Sy);
+                Sxx = warp_sum(Sxx); Sxy = warp_sum(Sxy); Syy = warp_sum(Syy);
+                if (lane == 0) {
+                    float* out = v_splats + (size_t)stage[j].id * SPLAT_F;
+                    const float v_mx = a.z * Sx + a.w * Sy, v_my = a.w * Sx + b.x * Sy;
+                    red_add_v4(out, v_mx, v_my, 0.5f * Sxx, Sxy);
+                    if (HAS_RGB) {
+                        red_add_v4(out + 4, 0.5f * Syy, g_o, g_col[0], g_col[1]);
+                        if (HAS_D) red_add_v2(out + 8, g_col[2], g_col[3]);
+                        else atomicAdd(out + 8, g_col[2]);
+                    } else {
+                        red_add_v2(out + 4, 0.5f * Syy, g_o);
+                        atomicAdd(out + 9, g_col[0]);
+                    }
                 }
             }
         }
@@ -179,7 +201,10 @@ extern "C" int b200_raster_bwd(const float* splats, const int32_t* flatten_ids, 
     cudaStream_t st = (cudaStream_t)stream;
     const float4* sp = reinterpret_cast<const float4*>(splats);
     const int grid = (2 * n_tiles + RU_WARPS - 1) / RU_WARPS;
-#define LAUNCH(CS) raster_bwd_kernel<CS><<<grid, RU_THREADS, 0, st>>>(sp, flatten_ids, offsets, (int)M, width, height, tile_w, n_tiles, bg, alpha, last_ids, v_render, v_alpha, v_splats)
+    static int bfly = -1;
+    if (bfly < 0) { const char* e = getenv("B200_BWD_REDUCE"); bfly = (e && e[0] == '1') ? 1 : 0; }
+#define LAUNCH1(CS, BF) raster_bwd_kernel<CS, BF><<<grid, RU_THREADS, 0, st>>>(sp, flatten_ids, offsets, (int)M, width, height, tile_w, n_tiles, bg, alpha, last_ids, v_render, v_alpha, v_splats)
+#define LAUNCH(CS) do { if (bfly) LAUNCH1(CS, true); else LAUNCH1(CS, false); } while (0)
     switch (channels) {
         case B200_CH_RGB: LAUNCH(B200_CH_RGB); break;
         case B200_CH_D: LAUNCH(B200_CH_D); break;

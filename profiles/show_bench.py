@@ -1,0 +1,4 @@
+import json,sys
+l=json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
+print(sys.argv[1], round(l["value"],1), round(l["ms_per_step"],3), "e2e", round(l["e2e"]["value"],1))
+print("  "+" ".join(f"{k}={v['ms']}" for k,v in l["roofline"]["stages"].items()))
