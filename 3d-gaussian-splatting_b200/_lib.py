@@ -30,7 +30,8 @@ SIGNATURES = {
     "b200_version": (C.c_int, []),
     "b200_last_error": (C.c_char_p, []),
     "b200_project_blocks": (_l, [_l]),
-    "b200_project_sh_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p]),
+    "b200_cam_pack": (_i, [_p, _p, C.c_float, C.c_float, C.c_float, C.c_float, _i, _i, _p, _p]),
+    "b200_project_sh_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p]),
     "b200_sort_pairs_k32": (_i, [_p, _p, _p, _p, _l, _i, _p, _z, _p, _p]),
     "b200_sort_pairs_k16": (_i, [_p, _p, _p, _p, _l, _i, _p, _z, _p, _p]),
     "b200_bin_count_sorted": (_i, [_p, _p, _l, _p, _p]),
@@ -42,9 +43,9 @@ SIGNATURES = {
     "b200_sort_scratch_bytes": (_z, [_l]),
     "b200_sort_pairs": (_i, [_p, _p, _p, _p, _l, _i, _p, _z, _p, _p]),
     "b200_tile_ranges": (_i, [_p, _l, _i, _p, _p]),
-    "b200_raster_fwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _p, _p, _p, _p, _p]),
-    "b200_raster_bwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _p, _p, _p, _p, _p, _p, _p]),
-    "b200_project_sh_bwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "b200_raster_fwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _p, _i, _p, _p, _p, _p]),
+    "b200_raster_bwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _p, _i, _p, _p, _p, _p, _p, _p]),
+    "b200_project_sh_bwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
     "b200_densify_stats": (_i, [_p, _l, _p, _p, _p]),
 }
 
@@ -57,6 +58,7 @@ CH_RGB, CH_D, CH_RGBD = 0, 1, 2
 SPLAT_FLOATS = 12
 TILE = 16
 CAM_FLOATS = 24
+CAM_DEV_FLOATS = 32
 
 
 # Instrumentation used by bench.py: number of kernels of THIS library launched so far, and an optional

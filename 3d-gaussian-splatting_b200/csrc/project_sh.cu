@@ -7,6 +7,12 @@
 
 #define PROJ_THREADS 256
 
+// The camera block lives in constant memory (bank-addressed operands, no registers).  It is refreshed by a
+// stream-ordered copy in front of every projection launch — from the caller's packed DEVICE block
+// (b200_cam_pack; the pose never visits the host) or from a host block.  One slot: launches on a different
+// stream first wait for the last kernel that read it (load_cam / cam_used below).
+__constant__ Cam c_cam;
+
 namespace {
 
 constexpr float SH_C0 = 0.2820947917738781f;
@@ -160,10 +166,11 @@ template <int DEG>
 __global__ void __launch_bounds__(PROJ_THREADS)
 project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__ quats,
                       const float* __restrict__ scales, const float* __restrict__ opacities,
-                      const float* __restrict__ shs, int sh_coeffs, bool vec_ok, int64_t N, Cam cam,
+                      const float* __restrict__ shs, int sh_coeffs, bool vec_ok, int64_t N,
                       int32_t* __restrict__ radii, float* __restrict__ splats,
                       int32_t* __restrict__ tiles_per_gauss, int64_t* __restrict__ block_sums,
                       uint32_t* __restrict__ depth_keys, int32_t* __restrict__ gauss_ids) {
+    const Cam& cam = c_cam;
     int64_t g = (int64_t)blockIdx.x * PROJ_THREADS + threadIdx.x;
     int ntiles = 0;
     if (g < N) {
@@ -241,10 +248,11 @@ template <int DEG>
 __global__ void __launch_bounds__(PROJ_THREADS, 2)
 project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__ quats,
                       const float* __restrict__ scales, const float* __restrict__ opacities,
-                      const float* __restrict__ shs, int sh_coeffs, bool vec_ok, int64_t N, Cam cam,
+                      const float* __restrict__ shs, int sh_coeffs, bool vec_ok, int64_t N,
                       const int32_t* __restrict__ radii, const float* __restrict__ v_splats,
                       float* __restrict__ v_means, float* __restrict__ v_quats, float* __restrict__ v_scales,
                       float* __restrict__ v_opacities, float* __restrict__ v_shs) {
+    const Cam& cam = c_cam;
     int64_t g = (int64_t)blockIdx.x * PROJ_THREADS + threadIdx.x;
     if (g >= N) return;
     int2 rad = __ldg(reinterpret_cast<const int2*>(radii) + g);
@@ -421,7 +429,68 @@ project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__
     v_opacities[g] = vo;
 }
 
+// Builds the packed camera block on the device from a device-resident pose and intrinsics.
+__global__ void cam_pack_kernel(const float* __restrict__ viewmat, const float* __restrict__ K, float near_plane,
+                                float far_plane, float eps2d, float radius_clip, int W, int H, Cam* __restrict__ out) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    Cam cam;
+    for (int i = 0; i < 3; ++i) {
+        for (int j = 0; j < 3; ++j) cam.R[i * 3 + j] = viewmat[i * 4 + j];
+        cam.t[i] = viewmat[i * 4 + 3];
+    }
+    for (int j = 0; j < 3; ++j)
+        cam.campos[j] = -(cam.R[0 * 3 + j] * cam.t[0] + cam.R[1 * 3 + j] * cam.t[1] + cam.R[2 * 3 + j] * cam.t[2]);
+    cam.fx = K[0]; cam.fy = K[4]; cam.cx = K[2]; cam.cy = K[5];
+    cam.near_plane = near_plane; cam.far_plane = far_plane; cam.eps2d = eps2d; cam.radius_clip = radius_clip;
+    cam.W = W; cam.H = H;
+    cam.tile_w = (W + TILE - 1) / TILE;
+    cam.tile_h = (H + TILE - 1) / TILE;
+    *out = cam;
+}
+
+#define CAM_MAX_DEV 16
+cudaEvent_t g_cam_event[CAM_MAX_DEV];
+cudaStream_t g_cam_stream[CAM_MAX_DEV];
+bool g_cam_event_ok[CAM_MAX_DEV];
+
+// Stream-ordered refresh of c_cam.  Returns the device ordinal (for cam_used) or a negative error code.
+int load_cam(const float* cam_host, const float* cam_dev, int W, int H, cudaStream_t st) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= CAM_MAX_DEV) { b200_set_error("device ordinal %d out of range", dev); return B200_EARG; }
+    if (!g_cam_event_ok[dev]) {
+        if (cudaEventCreateWithFlags(&g_cam_event[dev], cudaEventDisableTiming) != cudaSuccess) return b200_check_launch("cam event");
+        g_cam_event_ok[dev] = true;
+        g_cam_stream[dev] = st;
+    } else if (g_cam_stream[dev] != st) {
+        cudaStreamWaitEvent(st, g_cam_event[dev], 0);  // the previous reader of c_cam ran on another stream
+    }
+    if (cam_dev) {
+        cudaMemcpyToSymbolAsync(c_cam, cam_dev, sizeof(Cam), 0, cudaMemcpyDeviceToDevice, st);
+    } else {
+        Cam cam = b200_make_cam(cam_host, W, H);
+        cudaMemcpyToSymbolAsync(c_cam, &cam, sizeof(Cam), 0, cudaMemcpyHostToDevice, st);
+    }
+    return dev;
+}
+
+void cam_used(int dev, cudaStream_t st) {
+    cudaEventRecord(g_cam_event[dev], st);
+    g_cam_stream[dev] = st;
+}
+
 }  // namespace
+
+static_assert(sizeof(Cam) <= B200_CAM_DEV_FLOATS * sizeof(float), "packed camera block too small");
+
+extern "C" int b200_cam_pack(const float* viewmat, const float* K, float near_plane, float far_plane, float eps2d,
+                             float radius_clip, int width, int height, float* cam_dev, void* stream) {
+    B200_REQUIRE(viewmat && K && cam_dev && width > 0 && height > 0, "bad argument");
+    B200_REQUIRE(((uintptr_t)cam_dev & 15) == 0, "misaligned cam_dev");
+    cam_pack_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(viewmat, K, near_plane, far_plane, eps2d, radius_clip, width, height,
+                                                        reinterpret_cast<Cam*>(cam_dev));
+    return b200_check_launch("cam_pack");
+}
 
 extern "C" int64_t b200_project_blocks(int64_t N) { return (N + PROJ_THREADS - 1) / PROJ_THREADS; }
 
@@ -432,20 +501,22 @@ static bool sh_args_ok(int sh_coeffs, int sh_degree) {
 
 extern "C" int b200_project_sh_fwd(const float* means, const float* quats, const float* scales,
                                    const float* opacities, const float* shs, int sh_coeffs, int sh_degree,
-                                   int64_t N, const float* cam_host, int width, int height, int32_t* radii,
-                                   float* splats, int32_t* tiles_per_gauss, int64_t* block_sums,
+                                   int64_t N, const float* cam_host, const float* cam_dev, int width, int height,
+                                   int32_t* radii, float* splats, int32_t* tiles_per_gauss, int64_t* block_sums,
                                    uint32_t* depth_keys, int32_t* gauss_ids, void* stream) {
     B200_REQUIRE(N >= 0 && width > 0 && height > 0, "bad sizes");
     B200_REQUIRE(sh_args_ok(sh_coeffs, sh_degree), "sh_degree/sh_coeffs mismatch");
     if (N == 0) return B200_OK;
-    B200_REQUIRE(means && quats && scales && opacities && shs && cam_host && radii && splats && tiles_per_gauss && block_sums, "null pointer");
+    B200_REQUIRE(means && quats && scales && opacities && shs && radii && splats && tiles_per_gauss && block_sums, "null pointer");
+    B200_REQUIRE((cam_host != nullptr) != (cam_dev != nullptr), "exactly one of cam_host / cam_dev");
     B200_REQUIRE(((uintptr_t)quats & 15) == 0 && ((uintptr_t)splats & 15) == 0 && ((uintptr_t)radii & 7) == 0, "misaligned pointer");
     B200_REQUIRE((depth_keys == nullptr) == (gauss_ids == nullptr), "depth_keys and gauss_ids go together");
-    Cam cam = b200_make_cam(cam_host, width, height);
     bool vec_ok = sh_degree >= 0 && ((sh_coeffs * 12) % 16 == 0) && (((uintptr_t)shs & 15) == 0);
     dim3 grid((unsigned)b200_project_blocks(N)), block(PROJ_THREADS);
     cudaStream_t st = (cudaStream_t)stream;
-#define LAUNCH(D) project_sh_fwd_kernel<D><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, cam, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids)
+    const int cdev = load_cam(cam_host, cam_dev, width, height, st);
+    if (cdev < 0) return cdev;
+#define LAUNCH(D) project_sh_fwd_kernel<D><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids)
     switch (sh_degree) {
         case 0: LAUNCH(0); break;
         case 1: LAUNCH(1); break;
@@ -454,24 +525,27 @@ extern "C" int b200_project_sh_fwd(const float* means, const float* quats, const
         default: LAUNCH(-1); break;
     }
 #undef LAUNCH
+    cam_used(cdev, st);
     return b200_check_launch("project_sh_fwd");
 }
 
 extern "C" int b200_project_sh_bwd(const float* means, const float* quats, const float* scales,
                                    const float* opacities, const float* shs, int sh_coeffs, int sh_degree,
-                                   int64_t N, const float* cam_host, int width, int height, const int32_t* radii,
-                                   const float* v_splats, float* v_means, float* v_quats, float* v_scales,
+                                   int64_t N, const float* cam_host, const float* cam_dev, int width, int height,
+                                   const int32_t* radii, const float* v_splats, float* v_means, float* v_quats, float* v_scales,
                                    float* v_opacities, float* v_shs, void* stream) {
     B200_REQUIRE(N >= 0 && width > 0 && height > 0, "bad sizes");
     B200_REQUIRE(sh_args_ok(sh_coeffs, sh_degree), "sh_degree/sh_coeffs mismatch");
     if (N == 0) return B200_OK;
-    B200_REQUIRE(means && quats && scales && opacities && shs && cam_host && radii && v_splats && v_means && v_quats && v_scales && v_opacities && v_shs, "null pointer");
+    B200_REQUIRE((cam_host != nullptr) != (cam_dev != nullptr), "exactly one of cam_host / cam_dev");
+    B200_REQUIRE(means && quats && scales && opacities && shs && radii && v_splats && v_means && v_quats && v_scales && v_opacities && v_shs, "null pointer");
     B200_REQUIRE(((uintptr_t)quats & 15) == 0 && ((uintptr_t)v_splats & 15) == 0 && ((uintptr_t)v_quats & 15) == 0 && ((uintptr_t)radii & 7) == 0, "misaligned pointer");
-    Cam cam = b200_make_cam(cam_host, width, height);
     bool vec_ok = sh_degree >= 0 && ((sh_coeffs * 12) % 16 == 0) && (((uintptr_t)shs & 15) == 0) && (((uintptr_t)v_shs & 15) == 0);
     dim3 grid((unsigned)b200_project_blocks(N)), block(PROJ_THREADS);
     cudaStream_t st = (cudaStream_t)stream;
-#define LAUNCH(D) project_sh_bwd_kernel<D><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, cam, radii, v_splats, v_means, v_quats, v_scales, v_opacities, v_shs)
+    const int cdev = load_cam(cam_host, cam_dev, width, height, st);
+    if (cdev < 0) return cdev;
+#define LAUNCH(D) project_sh_bwd_kernel<D><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, v_splats, v_means, v_quats, v_scales, v_opacities, v_shs)
     switch (sh_degree) {
         case 0: LAUNCH(0); break;
         case 1: LAUNCH(1); break;
@@ -480,5 +554,6 @@ extern "C" int b200_project_sh_bwd(const float* means, const float* quats, const
         default: LAUNCH(-1); break;
     }
 #undef LAUNCH
+    cam_used(cdev, st);
     return b200_check_launch("project_sh_bwd");
 }

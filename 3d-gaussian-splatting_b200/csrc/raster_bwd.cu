@@ -12,8 +12,8 @@ namespace {
 template <int CHSET, bool BFLY>
 __global__ void __launch_bounds__(RU_THREADS)
 raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__ flatten_ids,
-                  const int32_t* __restrict__ offsets, int M, int W, int H, int tile_w, int n_tiles, Bg bg,
-                  const float* __restrict__ alpha_in, const int32_t* __restrict__ last_ids,
+                  const int32_t* __restrict__ offsets, int M, int W, int H, int tile_w, int n_tiles,
+                  const float* __restrict__ background, int n_bg, const float* __restrict__ alpha_in, const int32_t* __restrict__ last_ids,
                   const float* __restrict__ v_render, const float* __restrict__ v_alpha,
                   float* __restrict__ v_splats) {
     constexpr int CH = ChInfo<CHSET>::CH;
@@ -30,6 +30,9 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
     const int x_base = tx * TILE, y_base = ty * TILE + half * 8;
     StagedSplat* stage = s_splat[wid];
     const int start = offsets[tile];
+    Bg bg;
+#pragma unroll
+    for (int c = 0; c < CH; ++c) bg.v[c] = (c < n_bg) ? __ldg(background + c) : 0.f;
 
     float px[RU_SLOTS], py[RU_SLOTS], T[RU_SLOTS], va_eff[RU_SLOTS], vr[RU_SLOTS][CH], buf[RU_SLOTS][CH];
     int bin_final[RU_SLOTS];
@@ -186,7 +189,7 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
 }  // namespace
 
 extern "C" int b200_raster_bwd(const float* splats, const int32_t* flatten_ids, const int32_t* offsets, int64_t M,
-                               int width, int height, int channels, const float* background_host,
+                               int width, int height, int channels, const float* background, int n_background,
                                const float* alpha, const int32_t* last_ids, const float* v_render,
                                const float* v_alpha, float* v_splats, void* stream) {
     B200_REQUIRE(width > 0 && height > 0 && M >= 0 && M < ((int64_t)1 << 31), "bad sizes");
@@ -196,14 +199,13 @@ extern "C" int b200_raster_bwd(const float* splats, const int32_t* flatten_ids, 
     B200_REQUIRE(((uintptr_t)splats & 15) == 0 && ((uintptr_t)v_splats & 15) == 0, "misaligned splats");
     const int tile_w = (width + TILE - 1) / TILE, tile_h = (height + TILE - 1) / TILE;
     const int n_tiles = tile_w * tile_h;
-    Bg bg;
-    for (int c = 0; c < 4; ++c) bg.v[c] = (background_host && c < b200_channels(channels)) ? background_host[c] : 0.f;
+    B200_REQUIRE(n_background >= 0 && n_background <= b200_channels(channels) && (n_background == 0 || background), "bad background");
     cudaStream_t st = (cudaStream_t)stream;
     const float4* sp = reinterpret_cast<const float4*>(splats);
     const int grid = (2 * n_tiles + RU_WARPS - 1) / RU_WARPS;
     static int bfly = -1;
     if (bfly < 0) { const char* e = getenv("B200_BWD_REDUCE"); bfly = (e && e[0] == '1') ? 1 : 0; }
-#define LAUNCH1(CS, BF) raster_bwd_kernel<CS, BF><<<grid, RU_THREADS, 0, st>>>(sp, flatten_ids, offsets, (int)M, width, height, tile_w, n_tiles, bg, alpha, last_ids, v_render, v_alpha, v_splats)
+#define LAUNCH1(CS, BF) raster_bwd_kernel<CS, BF><<<grid, RU_THREADS, 0, st>>>(sp, flatten_ids, offsets, (int)M, width, height, tile_w, n_tiles, background, n_background, alpha, last_ids, v_render, v_alpha, v_splats)
 #define LAUNCH(CS) do { if (bfly) LAUNCH1(CS, true); else LAUNCH1(CS, false); } while (0)
     switch (channels) {
         case B200_CH_RGB: LAUNCH(B200_CH_RGB); break;

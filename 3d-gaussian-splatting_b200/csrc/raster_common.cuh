@@ -20,15 +20,34 @@ template <> struct ChInfo<B200_CH_RGBD> { static constexpr int CH = 4; };
 
 struct Bg { float v[4]; };
 
+#define LOG2E_F 1.4426950408889634f
+#define LN2_F 0.6931471805599453f
+
+// Staged form of a splat record: the conic is pre-multiplied by log2(e) (and A, C halved) by the staging
+// lane, so the 32 consumers evaluate sigma in base-2 units and feed it straight to MUFU.EX2.
 struct __align__(16) StagedSplat {
-    float4 a;  // mx, my, A, B
-    float4 b;  // C, opacity, r, g
+    float4 a;  // mx, my, 0.5*A*log2e, B*log2e
+    float4 b;  // 0.5*C*log2e, opacity, r, g
     float2 c;  // b, depth
     int id;    // Gaussian index
     int idx;   // position in the sorted list
 };
 
-// sigma = 0.5*(A dx^2 + C dy^2) + B dx dy, with ONE fixed operation order shared by the forward and the
+__device__ __forceinline__ void stage_conic(float4& a, float4& b) {
+    a.z *= 0.5f * LOG2E_F;
+    a.w *= LOG2E_F;
+    b.x *= 0.5f * LOG2E_F;
+}
+
+// 2^x, flush-to-zero: one MUFU.EX2 without the denormal range fix-up (results below 2^-126 are far under
+// the 1/255 alpha threshold anyway).  Forward and backward share it, so they agree bit for bit.
+__device__ __forceinline__ float fast_ex2(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// sigma (times log2 e when fed the staged conic) = hA dx^2 + hC dy^2 + B dx dy, with ONE fixed operation order shared by the forward and the
 // backward kernel so that both make the same skip decision for a (pixel, Gaussian) pair.
 __device__ __forceinline__ float eval_sigma(float hA, float B, float hC, float dx, float dy) {
     float s = (hA * dx) * dx;

@@ -7,8 +7,8 @@ namespace {
 template <int CHSET>
 __global__ void __launch_bounds__(RU_THREADS)
 raster_fwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__ flatten_ids,
-                  const int32_t* __restrict__ offsets, int M, int W, int H, int tile_w, int n_tiles, Bg bg,
-                  float* __restrict__ render, float* __restrict__ alpha_out, int32_t* __restrict__ last_ids) {
+                  const int32_t* __restrict__ offsets, int M, int W, int H, int tile_w, int n_tiles,
+                  const float* __restrict__ background, int n_bg, float* __restrict__ render, float* __restrict__ alpha_out, int32_t* __restrict__ last_ids) {
     constexpr int CH = ChInfo<CHSET>::CH;
     constexpr bool HAS_RGB = (CHSET != B200_CH_D);
     constexpr bool HAS_D = (CHSET != B200_CH_RGB);
@@ -49,9 +49,11 @@ raster_fwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
         if (idx_l < end) {
             const int g = __ldg(flatten_ids + idx_l);
             const float4* rec = splats + 3 * (size_t)g;
-            const float4 a = __ldg(rec), b = __ldg(rec + 1), c = __ldg(rec + 2);
+            float4 a = __ldg(rec), b = __ldg(rec + 1);
+            const float4 c = __ldg(rec + 2);
             keep = splat_reaches_box(a, b, bx0, bx1, by0, by1);
             if (keep) {
+                stage_conic(a, b);
                 stage[lane].a = a;
                 stage[lane].b = b;
                 stage[lane].c = make_float2(c.x, c.y);
@@ -65,14 +67,13 @@ raster_fwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
             mask &= mask - 1;
             const float4 a = stage[j].a;
             const float4 b = stage[j].b;
-            const float hA = 0.5f * a.z, hC = 0.5f * b.x;
             float al[RU_SLOTS];
             unsigned act = 0, any = 0;
 #pragma unroll
             for (int s = 0; s < RU_SLOTS; ++s) {
                 const float dx = a.x - px[s], dy = a.y - py[s];
-                const float sigma = eval_sigma(hA, a.w, hC, dx, dy);
-                const float vis = __expf(-sigma);
+                const float sigma = eval_sigma(a.z, a.w, b.x, dx, dy);  // base-2 units
+                const float vis = fast_ex2(-sigma);
                 al[s] = fminf(MAX_ALPHA, b.y * vis);
                 const bool ok = !(done & (1u << s)) && sigma >= 0.f && al[s] >= ALPHA_THRESHOLD;
                 if (ok) act |= 1u << s;
@@ -100,6 +101,9 @@ raster_fwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
         }
         __syncwarp();
     }
+    Bg bg;
+#pragma unroll
+    for (int c = 0; c < CH; ++c) bg.v[c] = (c < n_bg) ? __ldg(background + c) : 0.f;
 #pragma unroll
     for (int s = 0; s < RU_SLOTS; ++s) {
         const int ix = x_base + (s & 1) * 8 + lx, iy = y_base + (s >> 1) * 4 + ly;
@@ -125,8 +129,8 @@ int b200_channels(int chset) {
 }
 
 extern "C" int b200_raster_fwd(const float* splats, const int32_t* flatten_ids, const int32_t* offsets, int64_t M,
-                               int width, int height, int channels, const float* background_host, float* render,
-                               float* alpha, int32_t* last_ids, void* stream) {
+                               int width, int height, int channels, const float* background, int n_background,
+                               float* render, float* alpha, int32_t* last_ids, void* stream) {
     B200_REQUIRE(width > 0 && height > 0 && M >= 0 && M < ((int64_t)1 << 31), "bad sizes");
     B200_REQUIRE(b200_channels(channels) > 0, "bad channel set");
     B200_REQUIRE(offsets && render && alpha && last_ids, "null pointer");
@@ -134,12 +138,11 @@ extern "C" int b200_raster_fwd(const float* splats, const int32_t* flatten_ids, 
     B200_REQUIRE(((uintptr_t)splats & 15) == 0, "misaligned splats");
     const int tile_w = (width + TILE - 1) / TILE, tile_h = (height + TILE - 1) / TILE;
     const int n_tiles = tile_w * tile_h;
-    Bg bg;
-    for (int c = 0; c < 4; ++c) bg.v[c] = (background_host && c < b200_channels(channels)) ? background_host[c] : 0.f;
+    B200_REQUIRE(n_background >= 0 && n_background <= b200_channels(channels) && (n_background == 0 || background), "bad background");
     cudaStream_t st = (cudaStream_t)stream;
     const float4* sp = reinterpret_cast<const float4*>(splats);
     const int grid = (2 * n_tiles + RU_WARPS - 1) / RU_WARPS;
-#define LAUNCH(CS) raster_fwd_kernel<CS><<<grid, RU_THREADS, 0, st>>>(sp, flatten_ids, offsets, (int)M, width, height, tile_w, n_tiles, bg, render, alpha, last_ids)
+#define LAUNCH(CS) raster_fwd_kernel<CS><<<grid, RU_THREADS, 0, st>>>(sp, flatten_ids, offsets, (int)M, width, height, tile_w, n_tiles, background, n_background, render, alpha, last_ids)
     switch (channels) {
         case B200_CH_RGB: LAUNCH(B200_CH_RGB); break;
         case B200_CH_D: LAUNCH(B200_CH_D); break;

@@ -63,14 +63,25 @@ def _require_cuda(*tensors: torch.Tensor) -> torch.device:
     return dev
 
 
-def make_cam(viewmat: torch.Tensor, K: torch.Tensor, near_plane: float = 0.01, far_plane: float = 1e10,
-             eps2d: float = 0.3, radius_clip: float = 0.0):
-    """24-float host camera block of include/b200splat.h (B200_CAM_FLOATS)."""
-    vm = viewmat.detach().to(dtype=torch.float32, device="cpu").reshape(16).tolist()
-    Kc = K.detach().to(dtype=torch.float32, device="cpu")
-    vals = vm + [float(Kc[0, 0]), float(Kc[1, 1]), float(Kc[0, 2]), float(Kc[1, 2]),
-                 float(near_plane), float(far_plane), float(eps2d), float(radius_clip)]
-    return (C.c_float * _lib.CAM_FLOATS)(*vals)
+def make_cam(viewmat: torch.Tensor, K: torch.Tensor, width: int, height: int, near_plane: float = 0.01,
+             far_plane: float = 1e10, eps2d: float = 0.3, radius_clip: float = 0.0) -> torch.Tensor:
+    """Packed DEVICE camera block (include/b200splat.h, b200_cam_pack).  The pose and the intrinsics are
+    consumed on the device — like gsplat, which takes ``viewmats``/``Ks`` as CUDA tensors
+    (gsplat_backend.py:174-175) — so rendering a view never synchronises on them.  CPU tensors are uploaded."""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    if viewmat.device.type == "cuda":
+        dev = viewmat.device
+    elif K.device.type == "cuda":
+        dev = K.device
+    vm = viewmat.detach().to(device=dev, dtype=torch.float32).contiguous()
+    Kd = K.detach().to(device=dev, dtype=torch.float32).contiguous()
+    if vm.numel() != 16 or Kd.numel() != 9:
+        raise ValueError("make_cam: viewmat must be [4,4] and K [3,3]")
+    cam = torch.empty(_lib.CAM_DEV_FLOATS, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.b200_cam_pack(_ptr(vm), _ptr(Kd), float(near_plane), float(far_plane), float(eps2d),
+                                float(radius_clip), int(width), int(height), _ptr(cam), _stream()), "b200_cam_pack")
+    return cam
 
 
 def tile_n_bits(tile_w: int, tile_h: int) -> int:
@@ -115,7 +126,7 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
         gids_a = torch.empty(max(N, 1), dtype=torch.int32, device=dev)
     with _stage("project_sh_fwd"):
         check(lib.b200_project_sh_fwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors),
-                                      sh_coeffs, deg, N, cam, width, height, _ptr(radii), _ptr(splats),
+                                      sh_coeffs, deg, N, None, _ptr(cam), width, height, _ptr(radii), _ptr(splats),
                                       _ptr(tiles_per_gauss), _ptr(block_sums),
                                       _ptr(dkeys_a) if split else None, _ptr(gids_a) if split else None, st),
               "b200_project_sh_fwd", kernels=1 if N > 0 else 0)
@@ -213,14 +224,14 @@ class RasterizeSplats(torch.autograd.Function):
             render = torch.empty(height, width, nch, dtype=torch.float32, device=dev)
             alpha = torch.empty(height, width, 1, dtype=torch.float32, device=dev)
             last_ids = torch.empty(height, width, dtype=torch.int32, device=dev)
-            bg = (C.c_float * 4)(*([float(x) for x in background] + [0.0] * (4 - len(background))))
+            bg, n_bg = background  # device tensor (or None) and the number of channels it covers
             with _stage("raster_fwd"):
                 check(lib.b200_raster_fwd(_ptr(b["splats"]), _ptr(b["flatten_ids"]), _ptr(b["isect_offsets"]), b["M"],
-                                          width, height, chset, bg, _ptr(render), _ptr(alpha), _ptr(last_ids),
-                                          _stream()), "b200_raster_fwd")
+                                          width, height, chset, _ptr(bg), n_bg, _ptr(render), _ptr(alpha),
+                                          _ptr(last_ids), _stream()), "b200_raster_fwd")
         ctx.save_for_backward(means, quats, scales, opacities, colors, b["radii"], b["splats"], b["flatten_ids"],
                               b["isect_offsets"], alpha, last_ids)
-        ctx.cfg = (cam, width, height, sh_degree, chset, bg, b["M"])
+        ctx.cfg = (cam, width, height, sh_degree, chset, bg, n_bg, b["M"])
         ctx.mark_non_differentiable(b["radii"], b["splats"], b["tiles_per_gauss"], b["isect_ids"],
                                     b["flatten_ids"], b["isect_offsets"], last_ids)
         return (render, alpha, b["radii"], b["splats"], b["tiles_per_gauss"], b["isect_ids"], b["flatten_ids"],
@@ -230,7 +241,7 @@ class RasterizeSplats(torch.autograd.Function):
     @torch.amp.custom_bwd(device_type="cuda")
     def backward(ctx, v_render, v_alpha, *_unused):
         means, quats, scales, opacities, colors, radii, splats, flatten_ids, offsets, alpha, last_ids = ctx.saved_tensors
-        cam, width, height, sh_degree, chset, bg, M = ctx.cfg
+        cam, width, height, sh_degree, chset, bg, n_bg, M = ctx.cfg
         dev = means.device
         N = means.shape[0]
         nch = _NCH[chset]
@@ -243,8 +254,8 @@ class RasterizeSplats(torch.autograd.Function):
             st = _stream()
             v_splats = torch.zeros(N, _lib.SPLAT_FLOATS, dtype=torch.float32, device=dev)
             with _stage("raster_bwd"):
-                check(lib.b200_raster_bwd(_ptr(splats), _ptr(flatten_ids), _ptr(offsets), M, width, height, chset, bg,
-                                          _ptr(alpha), _ptr(last_ids), _ptr(v_render), _ptr(v_alpha), _ptr(v_splats),
+                check(lib.b200_raster_bwd(_ptr(splats), _ptr(flatten_ids), _ptr(offsets), M, width, height, chset,
+                                          _ptr(bg), n_bg, _ptr(alpha), _ptr(last_ids), _ptr(v_render), _ptr(v_alpha), _ptr(v_splats),
                                           st), "b200_raster_bwd")
             v_means = torch.empty_like(means)
             v_quats = torch.empty_like(quats)
@@ -257,7 +268,8 @@ class RasterizeSplats(torch.autograd.Function):
                 sh_coeffs, deg = colors.shape[1], int(sh_degree)
             with _stage("project_sh_bwd"):
                 check(lib.b200_project_sh_bwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors),
-                                              sh_coeffs, deg, N, cam, width, height, _ptr(radii), _ptr(v_splats),
+                                              sh_coeffs, deg, N, None, _ptr(cam), width, height, _ptr(radii),
+                                              _ptr(v_splats),
                                               _ptr(v_means), _ptr(v_quats), _ptr(v_scales), _ptr(v_opac),
                                               _ptr(v_colors), st), "b200_project_sh_bwd")
         return v_means, v_quats, v_scales, v_opac, v_colors, None, None, None, None, None, None, None, None
@@ -267,17 +279,15 @@ def _render_one(means, quats, scales, opacities, colors, viewmat, K, width, heig
                 background, near_plane, far_plane, eps2d, radius_clip, with_isect_ids=False, method="auto"):
     chset = _MODES[render_mode]
     nch = _NCH[chset]
-    if background is None:
-        bg = [0.0] * nch
+    # the background stays on the device (no host read-back); the depth channel composites over 0
+    if background is None or chset == _lib.CH_D:
+        bg = (None, 0)
     else:
-        bgl = [float(x) for x in background.detach().reshape(-1).to("cpu").tolist()]
-        if chset == _lib.CH_RGB:
-            bg = bgl[:3]
-        elif chset == _lib.CH_D:
-            bg = [0.0]
-        else:
-            bg = bgl[:3] + [0.0]  # depth channel composites over 0
-    cam = make_cam(viewmat, K, near_plane, far_plane, eps2d, radius_clip)
+        bgt = background.detach().reshape(-1).to(device=means.device, dtype=torch.float32).contiguous()
+        if bgt.numel() < 3:
+            raise ValueError("backgrounds must hold 3 colour channels")
+        bg = (bgt, 3)
+    cam = make_cam(viewmat, K, int(width), int(height), near_plane, far_plane, eps2d, radius_clip)
     out = RasterizeSplats.apply(means, quats, scales, opacities, colors, cam, int(width), int(height), sh_degree,
                                 chset, bg, with_isect_ids, method)
     render, alpha, radii, splats, tiles_per_gauss, isect_ids, flatten_ids, offsets, last_ids = out

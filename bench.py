@@ -282,7 +282,7 @@ def run_b200(args):
 
     # scene statistics for the last view (N_visible, M) and the per-stage roofline
     with torch.no_grad():
-        cam = pkg.make_cam(poses_dev[0], K)
+        cam = pkg.make_cam(poses_dev[0], K, W, H)
         b = pkg.project_and_bin(leaves["means3D"], leaves["rotations"], leaves["scales"],
                                 leaves["opacities"].squeeze(-1).contiguous(), leaves["shs"], deg, cam, W, H)
         M = b["M"]

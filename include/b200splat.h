@@ -49,13 +49,23 @@ extern "C" {
 #define B200_CH_D 1     /* "D" / "ED"       -> 1 channel (depth)    */
 #define B200_CH_RGBD 2  /* "RGB+D"/"RGB+ED" -> 4 channels (rgb, d)  */
 
-/* Camera block passed by value from the host: 16 viewmat floats (row-major 4x4 world->camera),
+/* Host camera block: 16 viewmat floats (row-major 4x4 world->camera),
  * then fx, fy, cx, cy (pixels; K[0,0],K[1,1],K[0,2],K[1,2] of gsplat_backend.py:10,175),
  * then near_plane, far_plane, eps2d, radius_clip (gsplat defaults 0.01, 1e10, 0.3, 0.0). */
 #define B200_CAM_FLOATS 24
+/* Packed DEVICE camera block (opaque, 16-B aligned) written by b200_cam_pack. */
+#define B200_CAM_DEV_FLOATS 32
 
 int b200_version(void);
 const char* b200_last_error(void);
+
+/* ---- stage 0: camera block built ON THE DEVICE ------------------------------------------------
+ * The reference hands the backend a device-resident pose (viewpoint['world_view_transform'],
+ * trainer.py:459-466) and device intrinsics (self.K, gsplat_backend.py:10,175); gsplat consumes both on
+ * the device.  b200_cam_pack does the same: viewmat[16] and K[9] are DEVICE pointers, no host sync.
+ * cam_dev[B200_CAM_DEV_FLOATS] is then passed to the projection stages (forward and backward). */
+int b200_cam_pack(const float* viewmat, const float* K, float near_plane, float far_plane, float eps2d,
+                  float radius_clip, int width, int height, float* cam_dev, void* stream);
 
 /* ---- stage 1: EWA projection + SH colour + per-Gaussian tile count (fused) -------------------
  * Replaces gsplat fully_fused_projection + spherical_harmonics + clamp_min(c+0.5,0) + the counting
@@ -65,11 +75,13 @@ const char* b200_last_error(void);
  * Outputs: radii[N,2] int32, splats[N,12], tiles_per_gauss[N] int32,
  *          block_sums[b200_project_blocks(N)] int64 (sum of tiles_per_gauss per 256-Gaussian block);
  *          optional (both or neither NULL) depth_keys[N] uint32 = fp32 depth bits (0xFFFFFFFF if culled)
- *          and gauss_ids[N] = 0..N-1, the input of the split-key sort below. */
+ *          and gauss_ids[N] = 0..N-1, the input of the split-key sort below.
+ * Camera: exactly one of cam_host (B200_CAM_FLOATS host floats) and cam_dev (b200_cam_pack output) is
+ * non-NULL; width/height must equal the ones the block was packed with. */
 int64_t b200_project_blocks(int64_t N);
 int b200_project_sh_fwd(const float* means, const float* quats, const float* scales,
                         const float* opacities, const float* shs, int sh_coeffs, int sh_degree,
-                        int64_t N, const float* cam_host, int width, int height,
+                        int64_t N, const float* cam_host, const float* cam_dev, int width, int height,
                         int32_t* radii, float* splats, int32_t* tiles_per_gauss,
                         int64_t* block_sums, uint32_t* depth_keys, int32_t* gauss_ids, void* stream);
 
@@ -127,16 +139,17 @@ int b200_tile_ranges(const int64_t* sorted_isect_ids, int64_t M, int n_tiles, in
 
 /* ---- stage 3: forward blend (gsplat rasterize_to_pixels forward) ----------------------------
  * render[H,W,CH] alpha[H,W] last_ids[H,W] (index into the sorted list of the last composited
- * Gaussian, -1 if none).  background_host: CH floats or NULL (zeros). */
+ * Gaussian, -1 if none).  background: DEVICE pointer to n_background <= CH floats (the reference's
+ * bg_color tensor, trainer.py:471-478); channels beyond n_background composite over 0. */
 int b200_raster_fwd(const float* splats, const int32_t* flatten_ids, const int32_t* offsets,
-                    int64_t M, int width, int height, int channels, const float* background_host,
-                    float* render, float* alpha, int32_t* last_ids, void* stream);
+                    int64_t M, int width, int height, int channels, const float* background,
+                    int n_background, float* render, float* alpha, int32_t* last_ids, void* stream);
 
 /* ---- stage 4a: backward blend (gsplat rasterize_to_pixels backward) -------------------------
  * v_render[H,W,CH], v_alpha[H,W] or NULL.  ACCUMULATES into v_splats[N,12] (caller zeroes). */
 int b200_raster_bwd(const float* splats, const int32_t* flatten_ids, const int32_t* offsets,
-                    int64_t M, int width, int height, int channels, const float* background_host,
-                    const float* alpha, const int32_t* last_ids, const float* v_render,
+                    int64_t M, int width, int height, int channels, const float* background,
+                    int n_background, const float* alpha, const int32_t* last_ids, const float* v_render,
                     const float* v_alpha, float* v_splats, void* stream);
 
 /* ---- stage 4b: projection + SH backward ----------------------------------------------------
@@ -144,7 +157,7 @@ int b200_raster_bwd(const float* splats, const int32_t* flatten_ids, const int32
  * accumulate) v_means[N,3] v_quats[N,4] v_scales[N,3] v_opacities[N] v_shs[N,sh_coeffs,3]. */
 int b200_project_sh_bwd(const float* means, const float* quats, const float* scales,
                         const float* opacities, const float* shs, int sh_coeffs, int sh_degree,
-                        int64_t N, const float* cam_host, int width, int height,
+                        int64_t N, const float* cam_host, const float* cam_dev, int width, int height,
                         const int32_t* radii, const float* v_splats,
                         float* v_means, float* v_quats, float* v_scales, float* v_opacities,
                         float* v_shs, void* stream);

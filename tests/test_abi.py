@@ -39,7 +39,7 @@ def test_bad_arguments_are_rejected_without_touching_the_gpu(pkg):
     lib = pkg._lib.lib
     rc = lib.b200_sort_pairs(None, None, None, None, 10, 45, None, 0, None, None)
     assert rc == -1 and b"null" in lib.b200_last_error()
-    rc = lib.b200_raster_fwd(None, None, None, 0, 0, 0, 0, None, None, None, None, None)
+    rc = lib.b200_raster_fwd(None, None, None, 0, 0, 0, 0, None, 0, None, None, None, None)
     assert rc == -1
 
 

@@ -103,7 +103,7 @@ def test_split_key_binning_bit_exact(pkg, oracle, N, W, H):
     same sorted keys / ids / ranges as a stable sort of the 64-bit keys."""
     sc, act = _scene(oracle, N, W, H, seed=3)
     a = _cuda(act)
-    cam = pkg.make_cam(sc["viewmat"], sc["K"])
+    cam = pkg.make_cam(sc["viewmat"], sc["K"], W, H)
     b = pkg.project_and_bin(a["means3D"], a["rotations"], a["scales"], a["opacities"].squeeze(-1).contiguous(),
                             a["shs"], 3, cam, W, H, method="split", with_isect_ids=True)
     sp, radii = b["splats"].cpu(), b["radii"].cpu()
@@ -126,7 +126,7 @@ def test_split_key_ties_keep_gaussian_order(pkg, oracle):
     sc, act = _scene(oracle, N, W, H, seed=13)
     act["means3D"][:, 2] = torch.tensor([3.0, 5.0, 7.0])[torch.arange(N) % 3]
     a = _cuda(act)
-    cam = pkg.make_cam(sc["viewmat"], sc["K"])
+    cam = pkg.make_cam(sc["viewmat"], sc["K"], W, H)
     b = pkg.project_and_bin(a["means3D"], a["rotations"], a["scales"], a["opacities"].squeeze(-1).contiguous(),
                             a["shs"], 3, cam, W, H, method="split", with_isect_ids=True)
     sp, radii = b["splats"].cpu(), b["radii"].cpu()
@@ -139,7 +139,7 @@ def test_split_key_ties_keep_gaussian_order(pkg, oracle):
 def test_binning_sort_ranges_bit_exact(pkg, oracle, N, W, H):
     sc, act = _scene(oracle, N, W, H, seed=3)
     a = _cuda(act)
-    cam = pkg.make_cam(sc["viewmat"], sc["K"])
+    cam = pkg.make_cam(sc["viewmat"], sc["K"], W, H)
     b = pkg.project_and_bin(a["means3D"], a["rotations"], a["scales"], a["opacities"].squeeze(-1).contiguous(),
                             a["shs"], 3, cam, W, H, keep_unsorted=True, method="keys64")
     sp = b["splats"].cpu()
@@ -161,7 +161,7 @@ def test_cum_tiles_output(pkg, oracle):
     sc, act = _scene(oracle, N, W, H, seed=5)
     a = _cuda(act)
     lib, L = pkg._lib.lib, pkg._lib
-    cam = pkg.make_cam(sc["viewmat"], sc["K"])
+    cam = pkg.make_cam(sc["viewmat"], sc["K"], W, H)
     b = pkg.project_and_bin(a["means3D"], a["rotations"], a["scales"], a["opacities"].squeeze(-1).contiguous(),
                             a["shs"], 3, cam, W, H)
     nb = lib.b200_project_blocks(N)
