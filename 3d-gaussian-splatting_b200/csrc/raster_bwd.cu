@@ -1,25 +1,72 @@
 // raster_bwd.cu — stage 4a: reverse replay of the blend and accumulation of the splat-record
 // cotangents (gsplat rasterize_to_pixels backward, triggered by the reference at
 // src/training/trainer.py:505-511).  Work decomposition: raster_common.cuh.  Each lane sums a
-// Gaussian's ten partial sums over its four pixels in registers, the warp reduces them once per
-// (Gaussian, half tile) with shuffles, and lane 0 issues three 16-byte vector REDs into the 48-B
-// gradient record — 3 L2 atomic operations per (Gaussian, half tile) instead of 10 per warp of 32 px.
+// Gaussian's ten partial sums over its four pixels in registers and parks them in shared memory; every
+// RB_GROUP Gaussians the warp reduces the parked block with a transposed read (flush_pending) and issues
+// three 16-byte vector REDs per Gaussian into the 48-B gradient record — 3 L2 atomic operations per
+// (Gaussian, half tile) instead of 10 per warp of 32 px, and no shuffle trees.
 #include <stdlib.h>
 #include "raster_common.cuh"
 
 namespace {
 
-template <int CHSET, bool BFLY>
+#define RB_GROUP 4            // Gaussians whose per-lane partial sums wait in shared memory for one reduction
+#define RB_ROW (32 * 3)       // float4 per waiting Gaussian: 32 lanes x {q0, q1, q2}
+
+struct __align__(16) Pending { int id; float A, B, C; };
+
+// Reduction of RB_GROUP x 32 lanes x 12 partial sums through shared memory.  Lane (g, q, h) = (lane>>3,
+// (lane>>1)&3, lane&1) adds the float4 group q of Gaussian g over the 16 source lanes 2i+h — 16 LDS.128 +
+// 64 FADD for four Gaussians, one shuffle level to join the halves — and the 12 lanes with h == 0, q < 3 each
+// issue ONE 16-byte vector RED.  ~30 warp instructions per Gaussian instead of ~105 for ten shuffle trees.
+// Bank check (float4 units, 8 per wavefront): quarter-warp = one g, index (2i+h)*3 + q = 6i + 3h + q ->
+// distinct for the six active (q, h) pairs.
+__device__ __forceinline__ void flush_pending(const float4* __restrict__ part, const Pending* __restrict__ pend, int np,
+                                              int lane, float* __restrict__ v_splats) {
+    __syncwarp();
+    const int g = lane >> 3, q = (lane >> 1) & 3, h = lane & 1;
+    const bool live = q < 3 && g < np;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (live) {
+        const float4* row = part + g * RB_ROW + 3 * h + q;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const float4 v = row[6 * i];
+            acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+    }
+    acc.x += __shfl_xor_sync(0xffffffffu, acc.x, 1);
+    acc.y += __shfl_xor_sync(0xffffffffu, acc.y, 1);
+    acc.z += __shfl_xor_sync(0xffffffffu, acc.z, 1);
+    acc.w += __shfl_xor_sync(0xffffffffu, acc.w, 1);
+    if (live && h == 0) {
+        const Pending p = pend[g];
+        float4 o = acc;
+        if (q == 0) {  // (Sx, Sy, Sxx, Sxy) -> (v_mx, v_my, v_A, v_B)
+            o.x = p.A * acc.x + p.B * acc.y;
+            o.y = p.B * acc.x + p.C * acc.y;
+            o.z = 0.5f * acc.z;
+        } else if (q == 1) {  // (Syy, v_opacity, v_r, v_g)
+            o.x = 0.5f * acc.x;
+        }
+        red_add_v4(v_splats + (size_t)p.id * SPLAT_F + 4 * q, o.x, o.y, o.z, o.w);
+    }
+    __syncwarp();
+}
+
+template <int CHSET>
 __global__ void __launch_bounds__(RU_THREADS)
 raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__ flatten_ids,
                   const int32_t* __restrict__ offsets, int M, int W, int H, int tile_w, int n_tiles,
-                  const float* __restrict__ background, int n_bg, const float* __restrict__ alpha_in, const int32_t* __restrict__ last_ids,
-                  const float* __restrict__ v_render, const float* __restrict__ v_alpha,
-                  float* __restrict__ v_splats) {
+                  const float* __restrict__ background, int n_bg, const float* __restrict__ alpha_in,
+                  const int32_t* __restrict__ last_ids, const float* __restrict__ v_render,
+                  const float* __restrict__ v_alpha, float* __restrict__ v_splats) {
     constexpr int CH = ChInfo<CHSET>::CH;
     constexpr bool HAS_RGB = (CHSET != B200_CH_D);
     constexpr bool HAS_D = (CHSET != B200_CH_RGB);
     __shared__ StagedSplat s_splat[RU_WARPS][32];
+    __shared__ float4 s_part[RU_WARPS][RB_GROUP * RB_ROW];
+    __shared__ Pending s_pend[RU_WARPS][RB_GROUP];
 
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int unit = blockIdx.x * RU_WARPS + wid;
@@ -29,6 +76,8 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
     const int lx = lane & 7, ly = lane >> 3;
     const int x_base = tx * TILE, y_base = ty * TILE + half * 8;
     StagedSplat* stage = s_splat[wid];
+    float4* part = s_part[wid];
+    Pending* pend = s_pend[wid];
     const int start = offsets[tile];
     Bg bg;
 #pragma unroll
@@ -67,6 +116,7 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
     if (warp_last < start) return;
     const float bx0 = (float)x_base + 0.5f, bx1 = (float)min(x_base + 15, W - 1) + 0.5f;
     const float by0 = (float)y_base + 0.5f, by1 = (float)min(y_base + 7, H - 1) + 0.5f;
+    int np = 0;  // Gaussians waiting in `part` (warp-uniform)
 
     for (int hi = warp_last; hi >= start; hi -= 32) {
         const int idx_l = hi - lane;
@@ -74,9 +124,11 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
         if (idx_l >= start) {
             const int g = __ldg(flatten_ids + idx_l);
             const float4* rec = splats + 3 * (size_t)g;
-            const float4 a = __ldg(rec), b = __ldg(rec + 1), c = __ldg(rec + 2);
+            float4 a = __ldg(rec), b = __ldg(rec + 1);
+            const float4 c = __ldg(rec + 2);
             keep = splat_reaches_box(a, b, bx0, bx1, by0, by1);
             if (keep) {
+                stage_conic(a, b);
                 stage[lane].a = a;
                 stage[lane].b = b;
                 stage[lane].c = make_float2(c.x, c.y);
@@ -92,15 +144,14 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
             const float4 a = stage[j].a;
             const float4 b = stage[j].b;
             const int idx = stage[j].idx;
-            const float hA = 0.5f * a.z, hC = 0.5f * b.x;
             float dx[RU_SLOTS], dy[RU_SLOTS], vis[RU_SLOTS], al[RU_SLOTS];
             unsigned act = 0, any = 0;
 #pragma unroll
             for (int s = 0; s < RU_SLOTS; ++s) {
                 dx[s] = a.x - px[s];
                 dy[s] = a.y - py[s];
-                const float sigma = eval_sigma(hA, a.w, hC, dx[s], dy[s]);
-                vis[s] = __expf(-sigma);
+                const float sigma = eval_sigma(a.z, a.w, b.x, dx[s], dy[s]);  // base-2 units
+                vis[s] = fast_ex2(-sigma);
                 al[s] = fminf(MAX_ALPHA, b.y * vis[s]);
                 const bool ok = idx <= bin_final[s] && sigma >= 0.f && al[s] >= ALPHA_THRESHOLD;
                 if (ok) act |= 1u << s;
@@ -112,7 +163,7 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
             if (HAS_RGB) { col[0] = b.z; col[1] = b.w; col[2] = c2.x; }
             if (HAS_D) col[CH - 1] = c2.y;
             // per-lane partial sums over this lane's pixels: colour cotangents, opacity, and the moments
-            // S = sum v_sigma, Sx = sum v_sigma dx, ... from which conic / mean cotangents follow
+            // Sx = sum v_sigma dx, Sxx = sum v_sigma dx^2, ... from which conic / mean cotangents follow
             float g_col[CH], g_o = 0.f, Sx = 0.f, Sy = 0.f, Sxx = 0.f, Sxy = 0.f, Syy = 0.f;
 #pragma unroll
             for (int c = 0; c < CH; ++c) g_col[c] = 0.f;
@@ -142,48 +193,25 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
                     }
                 }
             }
-            if (BFLY) {
-            // one transposing reduction for eight sums, plain trees for the one or two that remain; then a
-                // single RED instruction: lane 4k adds total k to record slot k, lanes 1/2 add the extras.
-                float v8[8] = {Sx, Sy, Sxx, Sxy, Syy, g_o, HAS_RGB ? g_col[0] : 0.f, HAS_RGB ? g_col[1] : 0.f};
-                float tot = warp_reduce8_transposed(v8, lane);
-                float ex0 = 0.f, ex1 = 0.f;
-                if (HAS_RGB) ex0 = warp_sum(g_col[2]);
-                if (HAS_D) ex1 = warp_sum(g_col[CH - 1]);
-                const float other = __shfl_xor_sync(0xffffffffu, tot, 4);  // Sy for the Sx lanes and vice versa
-                const int k = lane >> 2;
-                float val = tot;
-                if (k == 0) val = a.z * tot + a.w * other;        // v_mx = A Sx + B Sy
-                else if (k == 1) val = b.x * tot + a.w * other;   // v_my = C Sy + B Sx
-                else if (k == 2 || k == 4) val = 0.5f * tot;      // v_A = Sxx / 2, v_C = Syy / 2
-                int slot = (lane & 3) == 0 ? k : -1;
-                if (!HAS_RGB && k >= 6) slot = -1;
-                if (lane == 1 && HAS_RGB) { slot = 8; val = ex0; }
-                if (lane == 2 && HAS_D) { slot = 9; val = ex1; }
-                if (slot >= 0) atomicAdd(v_splats + (size_t)stage[j].id * SPLAT_F + slot, val);
-            } else {
-#pragma unroll
-                for (int c = 0; c < CH; ++c) g_col[c] = warp_sum(g_col[c]);
-                g_o = warp_sum(g_o);
-                Sx = warp_sum(Sx); Sy = warp_sum(Sy);
-                Sxx = warp_sum(Sxx); Sxy = warp_sum(Sxy); Syy = warp_sum(Syy);
-                if (lane == 0) {
-                    float* out = v_splats + (size_t)stage[j].id * SPLAT_F;
-                    const float v_mx = a.z * Sx + a.w * Sy, v_my = a.w * Sx + b.x * Sy;
-                    red_add_v4(out, v_mx, v_my, 0.5f * Sxx, Sxy);
-                    if (HAS_RGB) {
-                        red_add_v4(out + 4, 0.5f * Syy, g_o, g_col[0], g_col[1]);
-                        if (HAS_D) red_add_v2(out + 8, g_col[2], g_col[3]);
-                        else atomicAdd(out + 8, g_col[2]);
-                    } else {
-                        red_add_v2(out + 4, 0.5f * Syy, g_o);
-                        atomicAdd(out + 9, g_col[0]);
-                    }
-                }
+            // park the lane's partials; the warp reduces RB_GROUP Gaussians at a time (flush_pending)
+            float4* row = part + np * RB_ROW + 3 * lane;
+            row[0] = make_float4(Sx, Sy, Sxx, Sxy);
+            row[1] = make_float4(Syy, g_o, HAS_RGB ? g_col[0] : 0.f, HAS_RGB ? g_col[1] : 0.f);
+            row[2] = make_float4(HAS_RGB ? g_col[2] : 0.f, HAS_D ? g_col[CH - 1] : 0.f, 0.f, 0.f);
+            if (lane == 0) {
+                Pending p;
+                p.id = stage[j].id;
+                p.A = a.z * (2.f * LN2_F); p.B = a.w * LN2_F; p.C = b.x * (2.f * LN2_F);  // undo stage_conic
+                pend[np] = p;
+            }
+            if (++np == RB_GROUP) {
+                flush_pending(part, pend, np, lane, v_splats);
+                np = 0;
             }
         }
         __syncwarp();
     }
+    if (np) flush_pending(part, pend, np, lane, v_splats);
 }
 
 }  // namespace
@@ -203,10 +231,7 @@ extern "C" int b200_raster_bwd(const float* splats, const int32_t* flatten_ids, 
     cudaStream_t st = (cudaStream_t)stream;
     const float4* sp = reinterpret_cast<const float4*>(splats);
     const int grid = (2 * n_tiles + RU_WARPS - 1) / RU_WARPS;
-    static int bfly = -1;
-    if (bfly < 0) { const char* e = getenv("B200_BWD_REDUCE"); bfly = (e && e[0] == '1') ? 1 : 0; }
-#define LAUNCH1(CS, BF) raster_bwd_kernel<CS, BF><<<grid, RU_THREADS, 0, st>>>(sp, flatten_ids, offsets, (int)M, width, height, tile_w, n_tiles, background, n_background, alpha, last_ids, v_render, v_alpha, v_splats)
-#define LAUNCH(CS) do { if (bfly) LAUNCH1(CS, true); else LAUNCH1(CS, false); } while (0)
+#define LAUNCH(CS) raster_bwd_kernel<CS><<<grid, RU_THREADS, 0, st>>>(sp, flatten_ids, offsets, (int)M, width, height, tile_w, n_tiles, background, n_background, alpha, last_ids, v_render, v_alpha, v_splats)
     switch (channels) {
         case B200_CH_RGB: LAUNCH(B200_CH_RGB); break;
         case B200_CH_D: LAUNCH(B200_CH_D); break;
