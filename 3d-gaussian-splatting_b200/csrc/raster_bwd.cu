@@ -54,8 +54,8 @@ __device__ __forceinline__ void flush_pending(const float4* __restrict__ part, c
     __syncwarp();
 }
 
-template <int CHSET>
-__global__ void __launch_bounds__(RU_THREADS)
+template <int CHSET, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
 raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__ flatten_ids,
                   const int32_t* __restrict__ offsets, int M, int W, int H, int tile_w, int n_tiles,
                   const float* __restrict__ background, int n_bg, const float* __restrict__ alpha_in,
@@ -64,12 +64,12 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
     constexpr int CH = ChInfo<CHSET>::CH;
     constexpr bool HAS_RGB = (CHSET != B200_CH_D);
     constexpr bool HAS_D = (CHSET != B200_CH_RGB);
-    __shared__ StagedSplat s_splat[RU_WARPS][32];
-    __shared__ float4 s_part[RU_WARPS][RB_GROUP * RB_ROW];
-    __shared__ Pending s_pend[RU_WARPS][RB_GROUP];
+    __shared__ StagedSplat s_splat[WARPS][32];
+    __shared__ float4 s_part[WARPS][RB_GROUP * RB_ROW];
+    __shared__ Pending s_pend[WARPS][RB_GROUP];
 
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int unit = blockIdx.x * RU_WARPS + wid;
+    const int unit = blockIdx.x * WARPS + wid;
     if (unit >= 2 * n_tiles) return;
     const int tile = unit >> 1, half = unit & 1;
     const int ty = tile / tile_w, tx = tile - ty * tile_w;
@@ -230,13 +230,16 @@ extern "C" int b200_raster_bwd(const float* splats, const int32_t* flatten_ids, 
     B200_REQUIRE(n_background >= 0 && n_background <= b200_channels(channels) && (n_background == 0 || background), "bad background");
     cudaStream_t st = (cudaStream_t)stream;
     const float4* sp = reinterpret_cast<const float4*>(splats);
-    const int grid = (2 * n_tiles + RU_WARPS - 1) / RU_WARPS;
-#define LAUNCH(CS) raster_bwd_kernel<CS><<<grid, RU_THREADS, 0, st>>>(sp, flatten_ids, offsets, (int)M, width, height, tile_w, n_tiles, background, n_background, alpha, last_ids, v_render, v_alpha, v_splats)
+    const int warps = b200_ru_warps("B200_BWD_WARPS", RU_WARPS);
+    const int grid = (2 * n_tiles + warps - 1) / warps;
+#define LAUNCH1(CS, WP) raster_bwd_kernel<CS, WP><<<grid, WP * 32, 0, st>>>(sp, flatten_ids, offsets, (int)M, width, height, tile_w, n_tiles, background, n_background, alpha, last_ids, v_render, v_alpha, v_splats)
+#define LAUNCH(CS) do { if (warps == 1) LAUNCH1(CS, 1); else if (warps == 2) LAUNCH1(CS, 2); else LAUNCH1(CS, 4); } while (0)
     switch (channels) {
         case B200_CH_RGB: LAUNCH(B200_CH_RGB); break;
         case B200_CH_D: LAUNCH(B200_CH_D); break;
         default: LAUNCH(B200_CH_RGBD); break;
     }
 #undef LAUNCH
+#undef LAUNCH1
     return b200_check_launch("raster_bwd");
 }

@@ -124,3 +124,4 @@ __device__ __forceinline__ float warp_reduce8_transposed(const float (&v)[8], in
 }
 
 int b200_channels(int chset);
+int b200_ru_warps(const char* env, int dflt);

@@ -1,21 +1,22 @@
 // raster_fwd.cu — stage 3: front-to-back alpha blend (gsplat rasterize_to_pixels
 // forward as reached from gsplat_backend.py:168-182).  Work decomposition: raster_common.cuh.
+#include <stdlib.h>
 #include "raster_common.cuh"
 
 namespace {
 
-template <int CHSET>
-__global__ void __launch_bounds__(RU_THREADS)
+template <int CHSET, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
 raster_fwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__ flatten_ids,
                   const int32_t* __restrict__ offsets, int M, int W, int H, int tile_w, int n_tiles,
                   const float* __restrict__ background, int n_bg, float* __restrict__ render, float* __restrict__ alpha_out, int32_t* __restrict__ last_ids) {
     constexpr int CH = ChInfo<CHSET>::CH;
     constexpr bool HAS_RGB = (CHSET != B200_CH_D);
     constexpr bool HAS_D = (CHSET != B200_CH_RGB);
-    __shared__ StagedSplat s_splat[RU_WARPS][32];
+    __shared__ StagedSplat s_splat[WARPS][32];
 
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int unit = blockIdx.x * RU_WARPS + wid;
+    const int unit = blockIdx.x * WARPS + wid;
     if (unit >= 2 * n_tiles) return;
     const int tile = unit >> 1, half = unit & 1;
     const int ty = tile / tile_w, tx = tile - ty * tile_w;
@@ -119,6 +120,13 @@ raster_fwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
 
 }  // namespace
 
+// Warps (half-tile work units) per CTA: 1, 2 or 4; overridable through the environment for tuning runs.
+int b200_ru_warps(const char* env, int dflt) {
+    const char* e = getenv(env);
+    int w = e ? atoi(e) : dflt;
+    return (w == 1 || w == 2) ? w : 4;
+}
+
 int b200_channels(int chset) {
     switch (chset) {
         case B200_CH_RGB: return 3;
@@ -141,13 +149,16 @@ extern "C" int b200_raster_fwd(const float* splats, const int32_t* flatten_ids, 
     B200_REQUIRE(n_background >= 0 && n_background <= b200_channels(channels) && (n_background == 0 || background), "bad background");
     cudaStream_t st = (cudaStream_t)stream;
     const float4* sp = reinterpret_cast<const float4*>(splats);
-    const int grid = (2 * n_tiles + RU_WARPS - 1) / RU_WARPS;
-#define LAUNCH(CS) raster_fwd_kernel<CS><<<grid, RU_THREADS, 0, st>>>(sp, flatten_ids, offsets, (int)M, width, height, tile_w, n_tiles, background, n_background, render, alpha, last_ids)
+    const int warps = b200_ru_warps("B200_FWD_WARPS", RU_WARPS);
+    const int grid = (2 * n_tiles + warps - 1) / warps;
+#define LAUNCH1(CS, WP) raster_fwd_kernel<CS, WP><<<grid, WP * 32, 0, st>>>(sp, flatten_ids, offsets, (int)M, width, height, tile_w, n_tiles, background, n_background, render, alpha, last_ids)
+#define LAUNCH(CS) do { if (warps == 1) LAUNCH1(CS, 1); else if (warps == 2) LAUNCH1(CS, 2); else LAUNCH1(CS, 4); } while (0)
     switch (channels) {
         case B200_CH_RGB: LAUNCH(B200_CH_RGB); break;
         case B200_CH_D: LAUNCH(B200_CH_D); break;
         default: LAUNCH(B200_CH_RGBD); break;
     }
 #undef LAUNCH
+#undef LAUNCH1
     return b200_check_launch("raster_fwd");
 }

@@ -221,21 +221,49 @@ def run_b200(args):
         if world > 1:
             flat = pkg.allreduce_gradients(params_list, world * V, flat=flat)
 
+    # e2e: every view's pose and ground-truth frame come from pinned HOST memory.  The upload of view k+1 runs
+    # on a copy stream while view k renders (double-buffered device slots, events both ways), as a training loop
+    # with a prefetching loader does; each view's copy is issued inside the timed region.
+    copy_stream = torch.cuda.Stream(device=dev)
+    gt_slot = [torch.empty(H, W, 3, device=dev) for _ in range(2)]
+    pose_slot = [torch.empty(4, 4, device=dev) for _ in range(2)]
+    ready_ev = [torch.cuda.Event() for _ in range(2)]
+    free_ev = [torch.cuda.Event() for _ in range(2)]
+    e2e_state = {"k": 0, "primed": False}
+
+    def upload(slot, view_idx):
+        copy_stream.wait_event(free_ev[slot])  # the last reader of this slot (view k-2's loss/backward) is done
+        with torch.cuda.stream(copy_stream):
+            gt_slot[slot].copy_(gt_host, non_blocking=True)
+            pose_slot[slot].copy_(pose_host[view_idx], non_blocking=True)
+            ready_ev[slot].record(copy_stream)
+
     def step_e2e(step):
         """through the public backend call with HOST buffers: pose + ground-truth frame uploaded from pinned
         memory every view, L1 loss, backward, loss read back (what trainer.py:270-281,485-497 does per view)."""
         nonlocal flat
+        cur = torch.cuda.current_stream()
         for p in params_list:
             p.grad = None
         tot = torch.zeros((), device=dev)
         for v in range(V):
-            pose = pose_host[view_index(step, v)].to(dev, non_blocking=True)
-            gt = gt_host.to(dev, non_blocking=True)
-            vp = {"world_view_transform": pose, "image_width": W, "image_height": H}
+            k = e2e_state["k"]
+            slot = k & 1
+            if not e2e_state["primed"]:
+                for sl in range(2):
+                    free_ev[sl].record(cur)
+                upload(slot, view_index(step, v))
+                e2e_state["primed"] = True
+            nv, ns = (v + 1, step) if v + 1 < V else (0, step + 1)
+            upload(slot ^ 1, view_index(ns, nv))  # prefetch the next view while this one renders
+            cur.wait_event(ready_ev[slot])
+            vp = {"world_view_transform": pose_slot[slot], "image_width": W, "image_height": H}
             res = backend.render_with_depth(leaves, vp, bg_color=bg, render_mode="RGB", device="cuda", sh_degree=deg)
-            loss = (res["render"] - gt).abs().mean()
+            loss = (res["render"] - gt_slot[slot]).abs().mean()
             loss.backward()
+            free_ev[slot].record(cur)
             tot = tot + loss.detach()
+            e2e_state["k"] = k + 1
         if world > 1:
             flat = pkg.allreduce_gradients(params_list, world * V, flat=flat)
         return float(tot.item())  # D2H read of the step's result
