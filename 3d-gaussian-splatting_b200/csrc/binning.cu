@@ -220,6 +220,115 @@ __global__ void tile_ranges_k16_kernel(const uint16_t* __restrict__ keys, int64_
         for (int t = cur + 1; t < n_tiles; ++t) offsets[t] = (int32_t)M;
 }
 
+
+// ---- tile_prep: per-tile counts from the corner-difference grid -> tile ranges + radix digit bases ----
+// One CTA.  grid_g[(tile_h+1) x (tile_w+1)] holds +1/-1 at the corners of every visible Gaussian's tile
+// rectangle (project_sh_fwd).  Its 2-D inclusive prefix sum is the number of intersections per tile; the
+// row-major exclusive scan of that is isect_offsets (what tile_ranges derives from the SORTED keys), and the
+// two 8-bit digit histograms of the tile-key sort follow from the same counts — so neither a histogram
+// pass nor a ranges pass over the M intersections is needed.
+#define PREP_THREADS 1024
+__global__ void __launch_bounds__(PREP_THREADS)
+tile_prep_kernel(const int32_t* __restrict__ grid_g, int tile_w, int tile_h, int32_t* __restrict__ offsets,
+                 int64_t* __restrict__ total, uint32_t* __restrict__ digit_base) {
+    extern __shared__ int s_grid[];
+    __shared__ int s_wtot[PREP_THREADS / 32];
+    __shared__ int s_h0[256];
+    __shared__ int s_hw[8];
+    __shared__ int s_total;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int stride = tile_w + 1, rows = tile_h + 1, cells = stride * rows, n_tiles = tile_w * tile_h;
+    for (int i = tid; i < cells; i += PREP_THREADS) s_grid[i] = grid_g[i];
+    __syncthreads();
+    // inclusive scan along x, one warp per row
+    for (int r = wid; r < rows; r += PREP_THREADS / 32) {
+        int carry = 0;
+        for (int x0 = 0; x0 < stride; x0 += 32) {
+            const int x = x0 + lane;
+            int v = (x < stride) ? s_grid[r * stride + x] : 0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int n = __shfl_up_sync(0xffffffffu, v, o);
+                if (lane >= o) v += n;
+            }
+            v += carry;
+            if (x < stride) s_grid[r * stride + x] = v;
+            carry = __shfl_sync(0xffffffffu, v, 31);
+        }
+    }
+    __syncthreads();
+    // inclusive scan along y, one thread per column
+    for (int x = tid; x < stride; x += PREP_THREADS) {
+        int acc = 0;
+        for (int r = 0; r < rows; ++r) {
+            acc += s_grid[r * stride + x];
+            s_grid[r * stride + x] = acc;
+        }
+    }
+    __syncthreads();
+    // row-major exclusive scan of the per-tile counts: thread t owns `per` consecutive tiles
+    const int per = (n_tiles + PREP_THREADS - 1) / PREP_THREADS;
+    const int t0 = tid * per, t1 = min(t0 + per, n_tiles);
+    int sum = 0;
+    for (int t = t0; t < t1; ++t) {
+        const int ty = t / tile_w, tx = t - ty * tile_w;
+        sum += s_grid[ty * stride + tx];
+    }
+    int inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    if (lane == 31) s_wtot[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        const int w = s_wtot[lane];
+        int winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int n = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o) winc += n;
+        }
+        s_wtot[lane] = winc - w;
+        if (lane == 31) { total[0] = (int64_t)winc; s_total = winc; }
+    }
+    __syncthreads();
+    int run = s_wtot[wid] + inc - sum;
+    for (int t = t0; t < t1; ++t) {
+        const int ty = t / tile_w, tx = t - ty * tile_w;
+        offsets[t] = run;
+        run += s_grid[ty * stride + tx];
+    }
+    // digit histogram of pass 0 (tile id & 255) and its exclusive scan
+    if (tid < 256) {
+        int h = 0;
+        for (int t = tid; t < n_tiles; t += 256) {
+            const int ty = t / tile_w, tx = t - ty * tile_w;
+            h += s_grid[ty * stride + tx];
+        }
+        s_h0[tid] = h;
+    }
+    __syncthreads();  // also orders the global `offsets` writes above for the reads below (same CTA)
+    if (tid < 256) {
+        int h = s_h0[tid], hinc = h;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int n = __shfl_up_sync(0xffffffffu, hinc, o);
+            if (lane >= o) hinc += n;
+        }
+        if (lane == 31) s_hw[wid] = hinc;
+        asm volatile("bar.sync 1, 256;" ::: "memory");  // named barrier over the 8 warps taking part
+        int woff = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) woff += (w < wid) ? s_hw[w] : 0;
+        digit_base[tid] = (uint32_t)(woff + hinc - h);
+        // pass 1 digit = tile id >> 8: tiles are already in digit order, so the base is the tile offset
+        const int t = tid << 8;
+        digit_base[256 + tid] = (uint32_t)((t < n_tiles) ? offsets[t] : s_total);
+    }
+}
+
 // sorted 64-bit keys of the literal formulation, rebuilt on request (parity tests / gsplat meta)
 __global__ void isect_ids_kernel(const uint16_t* __restrict__ tile_keys, const int32_t* __restrict__ flatten_ids,
                                  const float* __restrict__ splats, int64_t M, int64_t* __restrict__ isect_ids) {
@@ -307,4 +416,21 @@ extern "C" int b200_isect_ids(const uint16_t* sorted_tile_keys, const int32_t* f
     B200_REQUIRE(sorted_tile_keys && flatten_ids && splats && isect_ids, "null pointer");
     isect_ids_kernel<<<(unsigned)((M + 255) / 256), 256, 0, (cudaStream_t)stream>>>(sorted_tile_keys, flatten_ids, splats, M, isect_ids);
     return b200_check_launch("isect_ids");
+}
+
+extern "C" size_t b200_tile_prep_max_cells(void) { return (size_t)(200 * 1024) / sizeof(int32_t); }
+
+extern "C" int b200_tile_prep(const int32_t* tile_grid, int width, int height, int32_t* offsets, int64_t* total,
+                              uint32_t* digit_base, void* stream) {
+    B200_REQUIRE(width > 0 && height > 0 && tile_grid && offsets && total && digit_base, "bad args");
+    const int tile_w = (width + TILE - 1) / TILE, tile_h = (height + TILE - 1) / TILE;
+    const size_t cells = (size_t)(tile_w + 1) * (size_t)(tile_h + 1);
+    B200_REQUIRE((int64_t)tile_w * tile_h <= 65536 && cells <= b200_tile_prep_max_cells(), "tile grid too large for tile_prep");
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(tile_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        attr_set = true;
+    }
+    tile_prep_kernel<<<1, PREP_THREADS, cells * sizeof(int32_t), (cudaStream_t)stream>>>(tile_grid, tile_w, tile_h, offsets, total, digit_base);
+    return b200_check_launch("tile_prep");
 }

@@ -169,7 +169,8 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
                       const float* __restrict__ shs, int sh_coeffs, bool vec_ok, int64_t N,
                       int32_t* __restrict__ radii, float* __restrict__ splats,
                       int32_t* __restrict__ tiles_per_gauss, int64_t* __restrict__ block_sums,
-                      uint32_t* __restrict__ depth_keys, int32_t* __restrict__ gauss_ids) {
+                      uint32_t* __restrict__ depth_keys, int32_t* __restrict__ gauss_ids,
+                      int32_t* __restrict__ tile_grid) {
     const Cam& cam = c_cam;
     int64_t g = (int64_t)blockIdx.x * PROJ_THREADS + threadIdx.x;
     int ntiles = 0;
@@ -217,6 +218,16 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
             int miny = (int)fminf(fmaxf(floorf(tile_y - try_), 0.f), fh);
             int maxy = (int)fminf(fmaxf(ceilf(tile_y + try_), 0.f), fh);
             ntiles = (maxy - miny) * (maxx - minx);
+            if (tile_grid != nullptr && ntiles > 0) {
+                // corner differences of the tile rectangle: a 2-D prefix sum (b200_tile_prep) turns the grid
+                // into per-tile intersection counts, i.e. the tile ranges and the radix digit histograms,
+                // without another pass over the M intersections
+                const int gs = cam.tile_w + 1;
+                atomicAdd(tile_grid + miny * gs + minx, 1);
+                atomicAdd(tile_grid + miny * gs + maxx, -1);
+                atomicAdd(tile_grid + maxy * gs + minx, -1);
+                atomicAdd(tile_grid + maxy * gs + maxx, 1);
+            }
         } else {
             rx = ry = 0;
         }
@@ -503,9 +514,13 @@ extern "C" int b200_project_sh_fwd(const float* means, const float* quats, const
                                    const float* opacities, const float* shs, int sh_coeffs, int sh_degree,
                                    int64_t N, const float* cam_host, const float* cam_dev, int width, int height,
                                    int32_t* radii, float* splats, int32_t* tiles_per_gauss, int64_t* block_sums,
-                                   uint32_t* depth_keys, int32_t* gauss_ids, void* stream) {
+                                   uint32_t* depth_keys, int32_t* gauss_ids, int32_t* tile_grid, void* stream) {
     B200_REQUIRE(N >= 0 && width > 0 && height > 0, "bad sizes");
     B200_REQUIRE(sh_args_ok(sh_coeffs, sh_degree), "sh_degree/sh_coeffs mismatch");
+    if (tile_grid != nullptr) {
+        const size_t cells = (size_t)((width + TILE - 1) / TILE + 1) * (size_t)((height + TILE - 1) / TILE + 1);
+        cudaMemsetAsync(tile_grid, 0, cells * sizeof(int32_t), (cudaStream_t)stream);
+    }
     if (N == 0) return B200_OK;
     B200_REQUIRE(means && quats && scales && opacities && shs && radii && splats && tiles_per_gauss && block_sums, "null pointer");
     B200_REQUIRE((cam_host != nullptr) != (cam_dev != nullptr), "exactly one of cam_host / cam_dev");
@@ -516,7 +531,7 @@ extern "C" int b200_project_sh_fwd(const float* means, const float* quats, const
     cudaStream_t st = (cudaStream_t)stream;
     const int cdev = load_cam(cam_host, cam_dev, width, height, st);
     if (cdev < 0) return cdev;
-#define LAUNCH(D) project_sh_fwd_kernel<D><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids)
+#define LAUNCH(D) project_sh_fwd_kernel<D><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid)
     switch (sh_degree) {
         case 0: LAUNCH(0); break;
         case 1: LAUNCH(1); break;

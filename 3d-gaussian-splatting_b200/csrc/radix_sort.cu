@@ -257,7 +257,8 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 template <typename KeyT>
 int sort_pairs_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_t* vals_b, int64_t M, int end_bit,
-                    void* scratch, size_t scratch_bytes, int* result_in_b_host, void* stream, const char* what) {
+                    void* scratch, size_t scratch_bytes, int* result_in_b_host, void* stream, const char* what,
+                    const uint32_t* prepared_base = nullptr) {
     if (!(M >= 0 && end_bit > 0 && end_bit <= (int)(8 * sizeof(KeyT)))) {
         b200_set_error("%s: bad sizes", what);
         return B200_EARG;
@@ -289,7 +290,11 @@ int sort_pairs_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_t* vals
     uint32_t* tickets = hist + RS_MAX_PASSES * RS_RADIX;
     uint32_t* status = tickets + 64;
     const size_t used = (RS_MAX_PASSES * RS_RADIX + 64) * sizeof(uint32_t) + (size_t)npasses * ntiles * RS_RADIX * sizeof(uint32_t);
-    cudaMemsetAsync(scratch, 0, used, st);
+    if (prepared_base == nullptr) {
+        cudaMemsetAsync(scratch, 0, used, st);
+    } else {  // digit bases supplied by the caller (b200_tile_prep): only tickets + status need clearing
+        cudaMemsetAsync(tickets, 0, used - RS_MAX_PASSES * RS_RADIX * sizeof(uint32_t), st);
+    }
     static int pad = -1;
     if (pad < 0) { const char* e = getenv("B200_SORT_SMEM_PAD"); pad = e ? atoi(e) : 0; }
     static int use_match = -1;
@@ -298,18 +303,21 @@ int sort_pairs_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_t* vals
     if (hb < 0) { const char* e = getenv("B200_HIST_BLOCKS"); hb = e ? atoi(e) : 148 * 2; }
     int hist_blocks = (int)min((int64_t)hb, (M + 255) / 256);
     const int hist_threads = (npasses <= 4) ? 256 : 128;  // warps * npasses <= RS_HIST_ROWS
-    rs_hist_kernel<KeyT><<<hist_blocks, hist_threads, 0, st>>>(keys_a, M, npasses, end_bit, hist);
-    rs_scan_kernel<<<npasses, RS_RADIX, 0, st>>>(hist);
+    if (prepared_base == nullptr) {
+        rs_hist_kernel<KeyT><<<hist_blocks, hist_threads, 0, st>>>(keys_a, M, npasses, end_bit, hist);
+        rs_scan_kernel<<<npasses, RS_RADIX, 0, st>>>(hist);
+    }
+    const uint32_t* bases = prepared_base ? prepared_base : hist;
     KeyT* kin = keys_a; uint32_t* vin = vals_a; KeyT* kout = keys_b; uint32_t* vout = vals_b;
     for (int p = 0; p < npasses; ++p) {
         int shift = p * RS_BITS;
         int bits = (end_bit - shift) < RS_BITS ? (end_bit - shift) : RS_BITS;
         if (use_match)
             rs_onesweep_kernel<KeyT, true><<<(unsigned)ntiles, RS_THREADS, sizeof(RsSmem<KeyT>) + pad, st>>>(
-                kin, vin, kout, vout, M, shift, bits, hist + p * RS_RADIX, status + (size_t)p * ntiles * RS_RADIX, tickets + p);
+                kin, vin, kout, vout, M, shift, bits, bases + p * RS_RADIX, status + (size_t)p * ntiles * RS_RADIX, tickets + p);
         else
             rs_onesweep_kernel<KeyT, false><<<(unsigned)ntiles, RS_THREADS, sizeof(RsSmem<KeyT>) + pad, st>>>(
-                kin, vin, kout, vout, M, shift, bits, hist + p * RS_RADIX, status + (size_t)p * ntiles * RS_RADIX, tickets + p);
+                kin, vin, kout, vout, M, shift, bits, bases + p * RS_RADIX, status + (size_t)p * ntiles * RS_RADIX, tickets + p);
         KeyT* tk = kin; kin = kout; kout = tk;
         uint32_t* tv = vin; vin = vout; vout = tv;
     }
@@ -340,4 +348,15 @@ extern "C" int b200_sort_pairs_k32(uint32_t* keys_a, uint32_t* vals_a, uint32_t*
 extern "C" int b200_sort_pairs_k16(uint16_t* keys_a, uint32_t* vals_a, uint16_t* keys_b, uint32_t* vals_b, int64_t M,
                                    int end_bit, void* scratch, size_t scratch_bytes, int* result_in_b_host, void* stream) {
     return sort_pairs_impl<uint16_t>(keys_a, vals_a, keys_b, vals_b, M, end_bit, scratch, scratch_bytes, result_in_b_host, stream, "b200_sort_pairs_k16");
+}
+
+extern "C" int b200_sort_pairs_k16_prepared(uint16_t* keys_a, uint32_t* vals_a, uint16_t* keys_b, uint32_t* vals_b, int64_t M,
+                                            int end_bit, const uint32_t* digit_base, void* scratch, size_t scratch_bytes,
+                                            int* result_in_b_host, void* stream) {
+    if (M > 0 && digit_base == nullptr) {
+        b200_set_error("b200_sort_pairs_k16_prepared: null digit_base");
+        return B200_EARG;
+    }
+    return sort_pairs_impl<uint16_t>(keys_a, vals_a, keys_b, vals_b, M, end_bit, scratch, scratch_bytes, result_in_b_host, stream,
+                                     "b200_sort_pairs_k16_prepared", digit_base);
 }

@@ -99,7 +99,10 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
 
     method "keys64": literal gsplat formulation — emit (tile<<32|depth) int64 keys, sort M pairs.
     method "split" (default when tile_w*tile_h <= 65536): same result, depth digits sorted over the N
-    Gaussians before duplication, 16-bit tile digits over the M intersections (include/b200splat.h).
+    Gaussians before duplication, 16-bit tile digits over the M intersections (include/b200splat.h); tile
+    ranges and digit histograms come from the corner-difference grid (b200_tile_prep).
+    method "split-hist": the split path with a histogram pass and tile_ranges over the sorted keys instead
+    (what "split" falls back to when the tile grid does not fit b200_tile_prep).
     """
     dev = means.device
     N = means.shape[0]
@@ -120,7 +123,10 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
     block_sums = torch.empty(max(nblocks, 1), dtype=torch.int64, device=dev)
     block_offsets = torch.empty(max(nblocks, 1), dtype=torch.int64, device=dev)
     total = torch.zeros(1, dtype=torch.int64, device=dev)
-    split = method == "split"
+    split = method in ("split", "split-hist")
+    # tile ranges + radix digit bases from the corner-difference grid (b200_tile_prep) when the grid fits
+    prep = method == "split" and (tile_w + 1) * (tile_h + 1) <= int(lib.b200_tile_prep_max_cells())
+    tile_grid = torch.empty((tile_h + 1) * (tile_w + 1), dtype=torch.int32, device=dev) if prep else None
     if split:
         dkeys_a = torch.empty(max(N, 1), dtype=torch.int32, device=dev)
         gids_a = torch.empty(max(N, 1), dtype=torch.int32, device=dev)
@@ -128,7 +134,8 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
         check(lib.b200_project_sh_fwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors),
                                       sh_coeffs, deg, N, None, _ptr(cam), width, height, _ptr(radii), _ptr(splats),
                                       _ptr(tiles_per_gauss), _ptr(block_sums),
-                                      _ptr(dkeys_a) if split else None, _ptr(gids_a) if split else None, st),
+                                      _ptr(dkeys_a) if split else None, _ptr(gids_a) if split else None,
+                                      _ptr(tile_grid), st),
               "b200_project_sh_fwd", kernels=1 if N > 0 else 0)
     out = dict(radii=radii, splats=splats, tiles_per_gauss=tiles_per_gauss, tile_w=tile_w, tile_h=tile_h)
     offsets = torch.empty(n_tiles, dtype=torch.int32, device=dev)
@@ -162,6 +169,12 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
         return out
 
     # ---- split-key path ----
+    if prep:
+        digit_base = torch.empty(512, dtype=torch.int32, device=dev)
+        total_prep = torch.empty(1, dtype=torch.int64, device=dev)
+        with _stage("tile_prep"):
+            check(lib.b200_tile_prep(_ptr(tile_grid), width, height, _ptr(offsets), _ptr(total_prep), _ptr(digit_base), st),
+                  "b200_tile_prep")
     dkeys_b = torch.empty_like(dkeys_a)
     gids_b = torch.empty_like(gids_a)
     scratch_n = _sort_scratch(N, dev)
@@ -186,13 +199,20 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
     scratch_m = _sort_scratch(M, dev)
     tbits = tile_n_bits(tile_w, tile_h)
     with _stage("sort_pairs"):
-        check(lib.b200_sort_pairs_k16(_ptr(tkeys_a), _ptr(vals_a), _ptr(tkeys_b), _ptr(vals_b), M, tbits,
-                                      _ptr(scratch_m), scratch_m.numel(), C.byref(in_b), st), "b200_sort_pairs_k16",
-              kernels=(2 + (tbits + 7) // 8) if M > 0 else 0)
+        if prep:
+            check(lib.b200_sort_pairs_k16_prepared(_ptr(tkeys_a), _ptr(vals_a), _ptr(tkeys_b), _ptr(vals_b), M, tbits,
+                                                   _ptr(digit_base), _ptr(scratch_m), scratch_m.numel(),
+                                                   C.byref(in_b), st), "b200_sort_pairs_k16_prepared",
+                  kernels=((tbits + 7) // 8) if M > 0 else 0)
+        else:
+            check(lib.b200_sort_pairs_k16(_ptr(tkeys_a), _ptr(vals_a), _ptr(tkeys_b), _ptr(vals_b), M, tbits,
+                                          _ptr(scratch_m), scratch_m.numel(), C.byref(in_b), st), "b200_sort_pairs_k16",
+                  kernels=(2 + (tbits + 7) // 8) if M > 0 else 0)
     tkeys_s, vals_s = (tkeys_b, vals_b) if in_b.value else (tkeys_a, vals_a)
-    with _stage("tile_ranges"):
-        check(lib.b200_tile_ranges_k16(_ptr(tkeys_s), M, n_tiles, _ptr(offsets), st), "b200_tile_ranges_k16",
-              kernels=1 if M > 0 else 0)
+    if not prep:
+        with _stage("tile_ranges"):
+            check(lib.b200_tile_ranges_k16(_ptr(tkeys_s), M, n_tiles, _ptr(offsets), st), "b200_tile_ranges_k16",
+                  kernels=1 if M > 0 else 0)
     out.update(M=M, flatten_ids=vals_s[:M], isect_offsets=offsets.view(tile_h, tile_w), tile_keys=tkeys_s[:M])
     if with_isect_ids:
         ids = torch.empty(max(M, 1), dtype=torch.int64, device=dev)

@@ -76,6 +76,8 @@ int b200_cam_pack(const float* viewmat, const float* K, float near_plane, float 
  *          block_sums[b200_project_blocks(N)] int64 (sum of tiles_per_gauss per 256-Gaussian block);
  *          optional (both or neither NULL) depth_keys[N] uint32 = fp32 depth bits (0xFFFFFFFF if culled)
  *          and gauss_ids[N] = 0..N-1, the input of the split-key sort below.
+ *          optional tile_grid[(tile_h+1)*(tile_w+1)] int32 (zeroed by this call): +1/-1 at the corners of
+ *          every visible Gaussian's tile rectangle, the input of b200_tile_prep.
  * Camera: exactly one of cam_host (B200_CAM_FLOATS host floats) and cam_dev (b200_cam_pack output) is
  * non-NULL; width/height must equal the ones the block was packed with. */
 int64_t b200_project_blocks(int64_t N);
@@ -83,7 +85,8 @@ int b200_project_sh_fwd(const float* means, const float* quats, const float* sca
                         const float* opacities, const float* shs, int sh_coeffs, int sh_degree,
                         int64_t N, const float* cam_host, const float* cam_dev, int width, int height,
                         int32_t* radii, float* splats, int32_t* tiles_per_gauss,
-                        int64_t* block_sums, uint32_t* depth_keys, int32_t* gauss_ids, void* stream);
+                        int64_t* block_sums, uint32_t* depth_keys, int32_t* gauss_ids,
+                        int32_t* tile_grid, void* stream);
 
 /* ---- stage 2a: exclusive scan of block sums; writes block_offsets[nblocks] and total[1] -------
  * (the cumsum half of gsplat isect_tiles).  Single CTA; nblocks = b200_project_blocks(N). */
@@ -127,6 +130,19 @@ int b200_bin_count_sorted(const int32_t* tiles_per_gauss, const int32_t* perm, i
 int b200_bin_emit_sorted(const float* splats, const int32_t* radii, const int32_t* tiles_per_gauss,
                          const int32_t* perm, const int64_t* block_offsets, int64_t N, int width,
                          int height, int64_t M, uint16_t* tile_keys, int32_t* flatten_ids, void* stream);
+/* Per-tile ranges and radix digit bases WITHOUT a pass over the intersections: the 2-D prefix sum of
+ * tile_grid (written by b200_project_sh_fwd) is the intersection count of every tile, so
+ *   offsets[n_tiles]  = row-major exclusive scan          (== b200_tile_ranges_k16 of the sorted keys),
+ *   total[0]          = M,
+ *   digit_base[2*256] = exclusive digit offsets of the two 8-bit passes of the tile-key sort
+ * come from one single-CTA kernel; b200_sort_pairs_k16_prepared then skips its histogram pass.
+ * Needs (tile_w+1)*(tile_h+1) <= b200_tile_prep_max_cells() (the grid is staged in shared memory). */
+size_t b200_tile_prep_max_cells(void);
+int b200_tile_prep(const int32_t* tile_grid, int width, int height, int32_t* offsets, int64_t* total,
+                   uint32_t* digit_base, void* stream);
+int b200_sort_pairs_k16_prepared(uint16_t* keys_a, uint32_t* vals_a, uint16_t* keys_b, uint32_t* vals_b,
+                                 int64_t M, int end_bit, const uint32_t* digit_base, void* scratch,
+                                 size_t scratch_bytes, int* result_in_b_host, void* stream);
 int b200_tile_ranges_k16(const uint16_t* sorted_tile_keys, int64_t M, int n_tiles, int32_t* offsets,
                          void* stream);
 int b200_isect_ids(const uint16_t* sorted_tile_keys, const int32_t* flatten_ids, const float* splats,

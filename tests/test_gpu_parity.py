@@ -118,6 +118,11 @@ def test_split_key_binning_bit_exact(pkg, oracle, N, W, H):
                               a["shs"], 3, cam, W, H, method="keys64")
     assert torch.equal(b64["flatten_ids"], b["flatten_ids"]) and torch.equal(b64["isect_ids"], b["isect_ids"])
     assert torch.equal(b64["isect_offsets"], b["isect_offsets"])
+    # and so does the split path with a histogram pass + ranges from the sorted keys (no tile_prep)
+    bh = pkg.project_and_bin(a["means3D"], a["rotations"], a["scales"], a["opacities"].squeeze(-1).contiguous(),
+                             a["shs"], 3, cam, W, H, method="split-hist")
+    assert bh["M"] == b["M"] and torch.equal(bh["flatten_ids"], b["flatten_ids"])
+    assert torch.equal(bh["isect_offsets"], b["isect_offsets"])
 
 
 def test_split_key_ties_keep_gaussian_order(pkg, oracle):
