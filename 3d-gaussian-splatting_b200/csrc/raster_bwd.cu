@@ -83,19 +83,20 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
 #pragma unroll
     for (int c = 0; c < CH; ++c) bg.v[c] = (c < n_bg) ? __ldg(background + c) : 0.f;
 
-    float px[RU_SLOTS], py[RU_SLOTS], T[RU_SLOTS], va_eff[RU_SLOTS], vr[RU_SLOTS][CH], buf[RU_SLOTS][CH];
+    // per-lane state of four pixels: transmittance, cotangents, and D = sum_c buffer_c * v_render_c (the only
+    // form in which the accumulated colour behind the current Gaussian is needed)
+    float T[RU_SLOTS], va_eff[RU_SLOTS], vr[RU_SLOTS][CH], D[RU_SLOTS];
     int bin_final[RU_SLOTS];
     int warp_last = -1;
 #pragma unroll
     for (int s = 0; s < RU_SLOTS; ++s) {
         const int ix = x_base + (s & 1) * 8 + lx, iy = y_base + (s >> 1) * 4 + ly;
-        px[s] = (float)ix + 0.5f;
-        py[s] = (float)iy + 0.5f;
         bin_final[s] = -1;
         T[s] = 1.f;
         va_eff[s] = 0.f;
+        D[s] = 0.f;
 #pragma unroll
-        for (int c = 0; c < CH; ++c) { vr[s][c] = 0.f; buf[s][c] = 0.f; }
+        for (int c = 0; c < CH; ++c) vr[s][c] = 0.f;
         if (ix < W && iy < H) {
             const size_t pix = (size_t)iy * W + ix;
             bin_final[s] = last_ids[pix];
@@ -114,6 +115,7 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
     }
     warp_last = __reduce_max_sync(0xffffffffu, warp_last);
     if (warp_last < start) return;
+    const float pxc = (float)(x_base + lx) + 4.5f, pyc = (float)(y_base + ly) + 2.5f;  // centroid of the 4 pixels
     const float bx0 = (float)x_base + 0.5f, bx1 = (float)min(x_base + 15, W - 1) + 0.5f;
     const float by0 = (float)y_base + 0.5f, by1 = (float)min(y_base + 7, H - 1) + 0.5f;
     int np = 0;  // Gaussians waiting in `part` (warp-uniform)
@@ -124,17 +126,9 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
         if (idx_l >= start) {
             const int g = __ldg(flatten_ids + idx_l);
             const float4* rec = splats + 3 * (size_t)g;
-            float4 a = __ldg(rec), b = __ldg(rec + 1);
-            const float4 c = __ldg(rec + 2);
+            const float4 a = __ldg(rec), b = __ldg(rec + 1), c = __ldg(rec + 2);
             keep = splat_reaches_box(a, b, bx0, bx1, by0, by1);
-            if (keep) {
-                stage_conic(a, b);
-                stage[lane].a = a;
-                stage[lane].b = b;
-                stage[lane].c = make_float2(c.x, c.y);
-                stage[lane].id = g;
-                stage[lane].idx = idx_l;
-            }
+            if (keep) stage_splat(stage[lane], a, b, c, g, idx_l);
         }
         unsigned mask = __ballot_sync(0xffffffffu, keep);
         __syncwarp();
@@ -144,24 +138,21 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
             const float4 a = stage[j].a;
             const float4 b = stage[j].b;
             const int idx = stage[j].idx;
-            float dx[RU_SLOTS], dy[RU_SLOTS], vis[RU_SLOTS], al[RU_SLOTS];
-            unsigned act = 0, any = 0;
+            const float u = a.x - pxc, v = a.y - pyc;
+            float sg[RU_SLOTS], vis[RU_SLOTS], al[RU_SLOTS];
+            eval_sigma4(a, b, u, v, sg);
+            bool ok[RU_SLOTS];
 #pragma unroll
             for (int s = 0; s < RU_SLOTS; ++s) {
-                dx[s] = a.x - px[s];
-                dy[s] = a.y - py[s];
-                const float sigma = eval_sigma(a.z, a.w, b.x, dx[s], dy[s]);  // base-2 units
-                vis[s] = fast_ex2(-sigma);
+                vis[s] = fast_ex2(-sg[s]);
                 al[s] = fminf(MAX_ALPHA, b.y * vis[s]);
-                const bool ok = idx <= bin_final[s] && sigma >= 0.f && al[s] >= ALPHA_THRESHOLD;
-                if (ok) act |= 1u << s;
-                if (__any_sync(0xffffffffu, ok)) any |= 1u << s;
+                ok[s] = al[s] >= ALPHA_THRESHOLD && sg[s] >= 0.f && idx <= bin_final[s];
             }
-            if (!any) continue;
-            const float2 c2 = stage[j].c;
+            if (!__any_sync(0xffffffffu, ok[0] || ok[1] || ok[2] || ok[3])) continue;
+            const float4 c4 = stage[j].c;
             float col[CH];
-            if (HAS_RGB) { col[0] = b.z; col[1] = b.w; col[2] = c2.x; }
-            if (HAS_D) col[CH - 1] = c2.y;
+            if (HAS_RGB) { col[0] = c4.x; col[1] = c4.y; col[2] = c4.z; }
+            if (HAS_D) col[CH - 1] = c4.w;
             // per-lane partial sums over this lane's pixels: colour cotangents, opacity, and the moments
             // Sx = sum v_sigma dx, Sxx = sum v_sigma dx^2, ... from which conic / mean cotangents follow
             float g_col[CH], g_o = 0.f, Sx = 0.f, Sy = 0.f, Sxx = 0.f, Sxy = 0.f, Syy = 0.f;
@@ -169,26 +160,28 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
             for (int c = 0; c < CH; ++c) g_col[c] = 0.f;
 #pragma unroll
             for (int s = 0; s < RU_SLOTS; ++s) {
-                if (!(any & (1u << s))) continue;  // warp-uniform
-                if (act & (1u << s)) {
+                if (ok[s]) {  // a slot no lane reaches is one untaken branch
                     const float ra = fast_rcp(1.f - al[s]);
                     T[s] *= ra;
                     const float fac = al[s] * T[s];
-                    float v_al = va_eff[s] * ra;
+                    float cv = 0.f;  // colour . v_render
 #pragma unroll
                     for (int c = 0; c < CH; ++c) {
                         g_col[c] = fmaf(fac, vr[s][c], g_col[c]);
-                        v_al = fmaf(col[c] * T[s] - buf[s][c] * ra, vr[s][c], v_al);
-                        buf[s][c] = fmaf(col[c], fac, buf[s][c]);
+                        cv = fmaf(col[c], vr[s][c], cv);
                     }
+                    // v_alpha = sum_c (col_c T - buffer_c / (1 - alpha)) v_render_c + T_final (v_a - bg.v_render) / (1 - alpha)
+                    const float v_al = fmaf(T[s], cv, ra * (va_eff[s] - D[s]));
+                    D[s] = fmaf(fac, cv, D[s]);
                     const float ov = b.y * vis[s];
                     if (ov <= MAX_ALPHA) {
+                        const float dx = (s & 1) ? u - 4.f : u + 4.f, dy = (s >> 1) ? v - 2.f : v + 2.f;
                         const float v_sigma = -ov * v_al;
-                        const float vx = v_sigma * dx[s], vy = v_sigma * dy[s];
+                        const float vx = v_sigma * dx, vy = v_sigma * dy;
                         Sx += vx; Sy += vy;
-                        Sxx = fmaf(vx, dx[s], Sxx);
-                        Sxy = fmaf(vx, dy[s], Sxy);
-                        Syy = fmaf(vy, dy[s], Syy);
+                        Sxx = fmaf(vx, dx, Sxx);
+                        Sxy = fmaf(vx, dy, Sxy);
+                        Syy = fmaf(vy, dy, Syy);
                         g_o = fmaf(vis[s], v_al, g_o);
                     }
                 }
@@ -201,7 +194,7 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
             if (lane == 0) {
                 Pending p;
                 p.id = stage[j].id;
-                p.A = a.z * (2.f * LN2_F); p.B = a.w * LN2_F; p.C = b.x * (2.f * LN2_F);  // undo stage_conic
+                p.A = a.z * (2.f * LN2_F); p.B = a.w * LN2_F; p.C = b.x * (2.f * LN2_F);  // undo the staging scale
                 pend[np] = p;
             }
             if (++np == RB_GROUP) {

@@ -3,7 +3,7 @@
 // Work decomposition (both directions): one WARP owns one half tile (16x8 px) of a 16x16 tile and
 // walks that tile's sorted list on its own — no block barriers.  The half tile is four 8x4 "slots";
 // lane l owns pixel (l & 7, l >> 3) of every slot, so a lane carries four pixels' state in registers
-// and a warp vote per slot skips sub-tiles a Gaussian does not reach.  Batches of 32 Gaussians are
+// and a slot whose 32 pixels a Gaussian does not reach costs one untaken branch.  Batches of 32 Gaussians are
 // gathered by the 32 lanes (three 16-B vectors per 48-B splat record), screened against the half
 // tile with an exact convex-quadratic bound, and only survivors are broadcast through shared memory.
 #pragma once
@@ -23,20 +23,25 @@ struct Bg { float v[4]; };
 #define LOG2E_F 1.4426950408889634f
 #define LN2_F 0.6931471805599453f
 
-// Staged form of a splat record: the conic is pre-multiplied by log2(e) (and A, C halved) by the staging
-// lane, so the 32 consumers evaluate sigma in base-2 units and feed it straight to MUFU.EX2.
+// Staged form of a splat record (64 B, four 16-B vectors).  The staging lane pre-multiplies the conic by
+// log2(e) (and halves A, C) so the 32 consumers evaluate sigma in base-2 units and feed it straight to
+// MUFU.EX2, and pre-computes the two constants of the four-slot expansion (eval_sigma4).
 struct __align__(16) StagedSplat {
-    float4 a;  // mx, my, 0.5*A*log2e, B*log2e
-    float4 b;  // 0.5*C*log2e, opacity, r, g
-    float2 c;  // b, depth
+    float4 a;  // mx, my, hA = 0.5*A*log2e, B' = B*log2e
+    float4 b;  // hC = 0.5*C*log2e, opacity, c0 = 16 hA + 4 hC, B8 = 8 B'
+    float4 c;  // r, g, b, depth
     int id;    // Gaussian index
     int idx;   // position in the sorted list
+    int pad0, pad1;
 };
 
-__device__ __forceinline__ void stage_conic(float4& a, float4& b) {
-    a.z *= 0.5f * LOG2E_F;
-    a.w *= LOG2E_F;
-    b.x *= 0.5f * LOG2E_F;
+// in: a = (mx, my, A, B), b = (C, opacity, r, g), c = (blue, depth, ., .) as stored in the splat record
+__device__ __forceinline__ void stage_splat(StagedSplat& st, float4 a, float4 b, const float4 c, int id, int idx) {
+    const float hA = a.z * (0.5f * LOG2E_F), Bp = a.w * LOG2E_F, hC = b.x * (0.5f * LOG2E_F);
+    st.a = make_float4(a.x, a.y, hA, Bp);
+    st.b = make_float4(hC, b.y, __fmaf_rn(16.f, hA, 4.f * hC), 8.f * Bp);
+    st.c = make_float4(b.z, b.w, c.x, c.y);
+    *reinterpret_cast<int2*>(&st.id) = make_int2(id, idx);
 }
 
 // 2^x, flush-to-zero: one MUFU.EX2 without the denormal range fix-up (results below 2^-126 are far under
@@ -47,8 +52,30 @@ __device__ __forceinline__ float fast_ex2(float x) {
     return r;
 }
 
-// sigma (times log2 e when fed the staged conic) = hA dx^2 + hC dy^2 + B dx dy, with ONE fixed operation order shared by the forward and the
-// backward kernel so that both make the same skip decision for a (pixel, Gaussian) pair.
+// sigma (base-2 units) at a lane's four pixels.  The pixels sit at (+-4, +-2) around their centroid, so
+// with (u, v) = mean - centroid:
+//   sigma(u + 4 sx, v + 2 sy) = [hA u^2 + hC v^2 + B u v] + c0 + sx 4(2 hA u + B v) + sy 2(2 hC v + B u) + sx sy 8B
+// 21 operations for four values instead of 4 x 9.  Slot s has sx = (s & 1) ? -1 : +1, sy = (s >> 1) ? -1 : +1
+// (d = mean - pixel, and the pixel of slot s is 8 (s & 1) to the right / 4 (s >> 1) below slot 0's).
+// Explicit round-to-nearest intrinsics pin ONE operation order (no contraction differences between the
+// forward and the backward kernel), so both make the same skip decision for a (pixel, Gaussian) pair.
+__device__ __forceinline__ void eval_sigma4(const float4 a, const float4 b, float u, float v, float (&s)[4]) {
+    const float hA = a.z, B = a.w, hC = b.x, c0 = b.z, B8 = b.w;
+    const float p = __fmul_rn(hA, u), q = __fmul_rn(hC, v), w = __fmul_rn(B, u);
+    const float sc = __fmaf_rn(p, u, __fmaf_rn(q, v, __fmul_rn(w, v)));
+    const float a4 = __fmaf_rn(2.f, p, __fmul_rn(B, v));  // (2 hA u + B v)
+    const float b2 = __fmaf_rn(2.f, q, w);                // (2 hC v + B u)
+    const float base = __fadd_rn(sc, c0);
+    const float P = __fadd_rn(base, B8), M = __fsub_rn(base, B8);
+    const float bb = __fmul_rn(2.f, b2);
+    const float t1 = __fmaf_rn(4.f, a4, bb), t2 = __fmaf_rn(4.f, a4, -bb);
+    s[0] = __fadd_rn(P, t1);
+    s[1] = __fsub_rn(M, t2);
+    s[2] = __fadd_rn(M, t2);
+    s[3] = __fsub_rn(P, t1);
+}
+
+// sigma = hA dx^2 + hC dy^2 + B dx dy at one point (used by the half-tile screen below).
 __device__ __forceinline__ float eval_sigma(float hA, float B, float hC, float dx, float dy) {
     float s = (hA * dx) * dx;
     s = fmaf(hC * dy, dy, s);

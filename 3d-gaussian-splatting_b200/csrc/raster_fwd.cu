@@ -24,42 +24,36 @@ raster_fwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
     const int x_base = tx * TILE, y_base = ty * TILE + half * 8;
     StagedSplat* stage = s_splat[wid];
 
-    float px[RU_SLOTS], py[RU_SLOTS], T[RU_SLOTS], acc[RU_SLOTS][CH];
+    // per-lane state of four pixels.  thr[s] is the alpha threshold of pixel s: 1/255 while it is live, +inf
+    // once it is finished (or lies outside the image) — the "done" test costs no instruction of its own.
+    float T[RU_SLOTS], acc[RU_SLOTS][CH], thr[RU_SLOTS];
     int last[RU_SLOTS];
-    unsigned done = 0;  // bit s: pixel of slot s finished (or outside the image)
+    const float INF = __int_as_float(0x7f800000);
 #pragma unroll
     for (int s = 0; s < RU_SLOTS; ++s) {
         const int ix = x_base + (s & 1) * 8 + lx, iy = y_base + (s >> 1) * 4 + ly;
-        px[s] = (float)ix + 0.5f;
-        py[s] = (float)iy + 0.5f;
         T[s] = 1.f;
         last[s] = -1;
 #pragma unroll
         for (int c = 0; c < CH; ++c) acc[s][c] = 0.f;
-        if (ix >= W || iy >= H) done |= 1u << s;
+        thr[s] = (ix >= W || iy >= H) ? INF : ALPHA_THRESHOLD;
     }
+    const float pxc = (float)(x_base + lx) + 4.5f, pyc = (float)(y_base + ly) + 2.5f;  // centroid of the 4 pixels
     const float bx0 = (float)x_base + 0.5f, bx1 = (float)min(x_base + 15, W - 1) + 0.5f;
     const float by0 = (float)y_base + 0.5f, by1 = (float)min(y_base + 7, H - 1) + 0.5f;
     const int start = offsets[tile];
     const int end = (tile + 1 < n_tiles) ? offsets[tile + 1] : M;
 
     for (int lo = start; lo < end; lo += 32) {
-        if (__all_sync(0xffffffffu, done == (1u << RU_SLOTS) - 1u)) break;
+        if (__all_sync(0xffffffffu, fminf(fminf(thr[0], thr[1]), fminf(thr[2], thr[3])) > 1.f)) break;
         const int idx_l = lo + lane;
         bool keep = false;
         if (idx_l < end) {
             const int g = __ldg(flatten_ids + idx_l);
             const float4* rec = splats + 3 * (size_t)g;
-            float4 a = __ldg(rec), b = __ldg(rec + 1);
-            const float4 c = __ldg(rec + 2);
+            const float4 a = __ldg(rec), b = __ldg(rec + 1), c = __ldg(rec + 2);
             keep = splat_reaches_box(a, b, bx0, bx1, by0, by1);
-            if (keep) {
-                stage_conic(a, b);
-                stage[lane].a = a;
-                stage[lane].b = b;
-                stage[lane].c = make_float2(c.x, c.y);
-                stage[lane].idx = idx_l;
-            }
+            if (keep) stage_splat(stage[lane], a, b, c, g, idx_l);
         }
         unsigned mask = __ballot_sync(0xffffffffu, keep);
         __syncwarp();
@@ -68,32 +62,27 @@ raster_fwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
             mask &= mask - 1;
             const float4 a = stage[j].a;
             const float4 b = stage[j].b;
-            float al[RU_SLOTS];
-            unsigned act = 0, any = 0;
+            float sg[RU_SLOTS], al[RU_SLOTS];
+            eval_sigma4(a, b, a.x - pxc, a.y - pyc, sg);
+            bool ok[RU_SLOTS];
 #pragma unroll
             for (int s = 0; s < RU_SLOTS; ++s) {
-                const float dx = a.x - px[s], dy = a.y - py[s];
-                const float sigma = eval_sigma(a.z, a.w, b.x, dx, dy);  // base-2 units
-                const float vis = fast_ex2(-sigma);
-                al[s] = fminf(MAX_ALPHA, b.y * vis);
-                const bool ok = !(done & (1u << s)) && sigma >= 0.f && al[s] >= ALPHA_THRESHOLD;
-                if (ok) act |= 1u << s;
-                if (__any_sync(0xffffffffu, ok)) any |= 1u << s;
+                al[s] = fminf(MAX_ALPHA, b.y * fast_ex2(-sg[s]));
+                ok[s] = al[s] >= thr[s] && sg[s] >= 0.f;
             }
-            if (!any) continue;
-            const float2 c2 = stage[j].c;
+            if (!__any_sync(0xffffffffu, ok[0] || ok[1] || ok[2] || ok[3])) continue;
+            const float4 col = stage[j].c;
             const int idx = stage[j].idx;
 #pragma unroll
             for (int s = 0; s < RU_SLOTS; ++s) {
-                if (!(any & (1u << s))) continue;  // warp-uniform
-                if (act & (1u << s)) {
+                if (ok[s]) {  // a slot no lane reaches is one untaken branch
                     const float Tn = T[s] * (1.f - al[s]);
                     if (Tn <= T_STOP) {
-                        done |= 1u << s;
+                        thr[s] = INF;
                     } else {
                         const float w = al[s] * T[s];
-                        if (HAS_RGB) { acc[s][0] += w * b.z; acc[s][1] += w * b.w; acc[s][2] += w * c2.x; }
-                        if (HAS_D) acc[s][CH - 1] += w * c2.y;
+                        if (HAS_RGB) { acc[s][0] += w * col.x; acc[s][1] += w * col.y; acc[s][2] += w * col.z; }
+                        if (HAS_D) acc[s][CH - 1] += w * col.w;
                         last[s] = idx;
                         T[s] = Tn;
                     }
