@@ -252,6 +252,7 @@ class RasterizeSplats(torch.autograd.Function):
         ctx.save_for_backward(means, quats, scales, opacities, colors, b["radii"], b["splats"], b["flatten_ids"],
                               b["isect_offsets"], alpha, last_ids)
         ctx.cfg = (cam, width, height, sh_degree, chset, bg, n_bg, b["M"])
+        ctx.set_materialize_grads(False)  # unused outputs hand backward() None instead of freshly zero-filled tensors
         ctx.mark_non_differentiable(b["radii"], b["splats"], b["tiles_per_gauss"], b["isect_ids"],
                                     b["flatten_ids"], b["isect_offsets"], last_ids)
         return (render, alpha, b["radii"], b["splats"], b["tiles_per_gauss"], b["isect_ids"], b["flatten_ids"],

@@ -36,6 +36,11 @@ def num_threads() -> int:
     return int(_lib.cpu_num_threads())
 
 
+def set_threads(n: int) -> None:
+    """Use ``n`` OpenMP threads from now on (overrides an inherited OMP_NUM_THREADS, e.g. torchrun's 1)."""
+    _lib.cpu_set_threads(int(n))
+
+
 def cam24(viewmat: torch.Tensor, K: torch.Tensor, near=0.01, far=1e10, eps2d=0.3, radius_clip=0.0) -> torch.Tensor:
     return torch.cat([viewmat.float().reshape(16), torch.tensor(
         [K[0, 0], K[1, 1], K[0, 2], K[1, 2], near, far, eps2d, radius_clip], dtype=torch.float32)]).contiguous()

@@ -49,6 +49,15 @@ static Cam make_cam(const float* c, int W, int H) {
     return cam;
 }
 
+/* launchers such as torchrun export OMP_NUM_THREADS=1; the timed baseline asks for the host cores explicitly */
+void cpu_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int cpu_num_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();
