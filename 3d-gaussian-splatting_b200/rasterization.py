@@ -84,6 +84,18 @@ def make_cam(viewmat: torch.Tensor, K: torch.Tensor, width: int, height: int, ne
     return cam
 
 
+_PINNED_M = {}
+
+
+def _pinned_scalar(dev: torch.device) -> torch.Tensor:
+    """One pinned int64 per device for the asynchronous read-back of the intersection count."""
+    t = _PINNED_M.get(dev)
+    if t is None:
+        t = torch.empty(1, dtype=torch.int64).pin_memory()
+        _PINNED_M[dev] = t
+    return t
+
+
 def tile_n_bits(tile_w: int, tile_h: int) -> int:
     return int(math.floor(math.log2(tile_w * tile_h))) + 1
 
@@ -175,6 +187,12 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
         with _stage("tile_prep"):
             check(lib.b200_tile_prep(_ptr(tile_grid), width, height, _ptr(offsets), _ptr(total_prep), _ptr(digit_base), st),
                   "b200_tile_prep")
+        # M is known here, before the depth sort: start its read-back now and collect it after the depth-sort
+        # launches are queued, so the host never waits on an idle GPU
+        m_host = _pinned_scalar(dev)
+        m_host.copy_(total_prep, non_blocking=True)
+        m_ready = torch.cuda.Event()
+        m_ready.record()
     dkeys_b = torch.empty_like(dkeys_a)
     gids_b = torch.empty_like(gids_a)
     scratch_n = _sort_scratch(N, dev)
@@ -187,7 +205,11 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
         check(lib.b200_bin_count_sorted(_ptr(tiles_per_gauss), _ptr(perm), N, _ptr(block_sums), st),
               "b200_bin_count_sorted", kernels=1 if N > 0 else 0)
         check(lib.b200_bin_scan(_ptr(block_sums), nblocks, _ptr(block_offsets), _ptr(total), st), "b200_bin_scan")
-    M = int(total.item())  # the one device->host sync of the forward pass (sizes the intersection buffers)
+    if prep:
+        m_ready.synchronize()  # the one host wait of the forward pass (sizes the intersection buffers)
+        M = int(m_host.item())
+    else:
+        M = int(total.item())
     tkeys_a = torch.empty(max(M, 1), dtype=torch.int16, device=dev)
     vals_a = torch.empty(max(M, 1), dtype=torch.int32, device=dev)
     with _stage("bin_emit"):
