@@ -337,6 +337,9 @@ def run_b200(args):
         "bin_emit": M * 12 + N * 16,
         "sort_pairs": M * 24,
         "tile_ranges": M * 8,
+        "tile_prep": ((W + 15) // 16 + 1) * ((H + 15) // 16 + 1) * 4 + ((W + 15) // 16) * ((H + 15) // 16) * 4,
+        "sort_depth": N * (4 + 4 * 16),   # one histogram read + four onesweep passes over (u32 key, i32 id)
+        "bin_scan": N * 8,
         "raster_fwd": M * 44 + W * H * 20,
         "raster_bwd": M * 44 + W * H * 24 + n_vis * 36,
         "project_sh_bwd": n_vis * 508 + (N - n_vis) * 200,
@@ -350,8 +353,15 @@ def run_b200(args):
     roofline = None
     if dom:
         ach = stages[dom]["GBps"]
+        traffic = None  # dram bytes per launch of the dominant kernel from the committed ncu capture of this config
+        try:
+            with open(os.path.join(ROOT, "profiles", f"ncu_traffic_config{args.config}.json")) as f:
+                traffic = json.load(f)["bytes"].get(dom)
+        except Exception:
+            pass
         roofline = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": round(ach / hbm, 4),
-                    "traffic": None, "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
+                    "traffic": traffic, "binding_resource": "FP32/SFU issue slots (not HBM) for raster_fwd / raster_bwd, see "
+                    "profiles/ncu_r01_summary.md" if dom.startswith("raster") else "HBM", "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
                     "share_of_step": round(per_view_ms[dom] / sum(per_view_ms.values()), 3), "stages": stages}
 
     cpu_baseline = None
