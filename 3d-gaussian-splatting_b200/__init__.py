@@ -9,9 +9,10 @@ from . import _lib  # noqa: F401  (raises ImportError if the CUDA library is not
 from .rasterization import rasterization, project_and_bin, RasterizeSplats, make_cam  # noqa: F401
 from .backend import B200Backend  # noqa: F401
 from .stats import densify_stats  # noqa: F401
+from .store import GaussianStore  # noqa: F401
 from .distributed import shard_views, allreduce_gradients, ViewShardedStep  # noqa: F401
 
 __all__ = [
-    "rasterization", "project_and_bin", "RasterizeSplats", "make_cam", "B200Backend", "densify_stats",
+    "rasterization", "project_and_bin", "RasterizeSplats", "make_cam", "B200Backend", "densify_stats", "GaussianStore",
     "shard_views", "allreduce_gradients", "ViewShardedStep",
 ]

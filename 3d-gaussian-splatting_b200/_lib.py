@@ -49,6 +49,8 @@ SIGNATURES = {
     "b200_raster_fwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _p, _i, _p, _p, _p, _p]),
     "b200_raster_bwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _p, _i, _p, _p, _p, _p, _p, _p]),
     "b200_project_sh_bwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "b200_project_sh_fwd_raw": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "b200_project_sh_bwd_raw": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _i, _p]),
     "b200_densify_stats": (_i, [_p, _l, _p, _p, _p]),
 }
 

@@ -162,7 +162,10 @@ __device__ __forceinline__ void load_sh(const float* __restrict__ shs, int64_t g
     }
 }
 
-template <int DEG>
+// RAW: the inputs are the reference's raw parameters (gaussian_model.py:65-76) and the getters' activations
+// (gaussian_model.py:90-108: exp / sigmoid; F.normalize is the quaternion normalisation done here anyway) are
+// applied in registers — no activated copies of the parameter store are ever materialised.
+template <int DEG, bool RAW>
 __global__ void __launch_bounds__(PROJ_THREADS)
 project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__ quats,
                       const float* __restrict__ scales, const float* __restrict__ opacities,
@@ -179,6 +182,10 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
         float4 q = __ldg(reinterpret_cast<const float4*>(quats) + g);
         float sx = __ldg(scales + 3 * g), sy = __ldg(scales + 3 * g + 1), sz = __ldg(scales + 3 * g + 2);
         float opac = __ldg(opacities + g);
+        if (RAW) {
+            sx = expf(sx); sy = expf(sy); sz = expf(sz);
+            opac = 1.f / (1.f + expf(-opac));
+        }
         Proj P;
         int rx = 0, ry = 0;
         bool ok = project_core(cam, px, py, pz, q, sx, sy, sz, P) && radius_and_cull(cam, P, opac, rx, ry);
@@ -255,7 +262,11 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
     }
 }
 
-template <int DEG>
+// MODE 0: activated inputs, gradients written.  MODE 1: raw parameters (see the forward kernel), gradients
+// w.r.t. the RAW parameters written.  MODE 2: raw parameters, gradients ACCUMULATED into the caller's buffers
+// (the flat gradient store): views after the first add in place, culled Gaussians and SH coefficients above
+// the active degree are not touched at all.
+template <int DEG, int MODE>
 __global__ void __launch_bounds__(PROJ_THREADS, 2)
 project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__ quats,
                       const float* __restrict__ scales, const float* __restrict__ opacities,
@@ -271,8 +282,10 @@ project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__
     float vm[3] = {0.f, 0.f, 0.f}, vq[4] = {0.f, 0.f, 0.f, 0.f}, vs[3] = {0.f, 0.f, 0.f}, vo = 0.f;
     const int ncoef_f = sh_coeffs * 3;
     float* vsh = (DEG >= 0) ? v_shs + g * (int64_t)ncoef_f : v_shs + 3 * g;
+    constexpr bool RAW = MODE != 0, ACC = MODE == 2;
 
     if (!vis) {
+        if (ACC) return;
         if (DEG >= 0) {
             if (vec_ok) {
                 float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -287,6 +300,7 @@ project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__
         float px = __ldg(means + 3 * g), py = __ldg(means + 3 * g + 1), pz = __ldg(means + 3 * g + 2);
         float4 q = __ldg(reinterpret_cast<const float4*>(quats) + g);
         float sx = __ldg(scales + 3 * g), sy = __ldg(scales + 3 * g + 1), sz = __ldg(scales + 3 * g + 2);
+        if (RAW) { sx = expf(sx); sy = expf(sy); sz = expf(sz); }
         const float4* vrec = reinterpret_cast<const float4*>(v_splats) + 3 * g;
         float4 g0 = __ldg(vrec), g1 = __ldg(vrec + 1), g2 = __ldg(vrec + 2);
         float v_mx = g0.x, v_my = g0.y, v_A = g0.z, v_B = g0.w, v_C = g1.x;
@@ -326,14 +340,25 @@ project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__
                         const int e = 4 * i + j, k = e / 3, ch = e - 3 * k;
                         o4[j] = (k < NB) ? B[k < NB ? k : 0] * vr[ch] : 0.f;
                     }
-                    reinterpret_cast<float4*>(vsh)[i] = make_float4(o4[0], o4[1], o4[2], o4[3]);
+                    if (ACC) {
+                        if (4 * i < 3 * NB) {
+                            float4 old = reinterpret_cast<float4*>(vsh)[i];
+                            reinterpret_cast<float4*>(vsh)[i] = make_float4(old.x + o4[0], old.y + o4[1], old.z + o4[2], old.w + o4[3]);
+                        }
+                    } else {
+                        reinterpret_cast<float4*>(vsh)[i] = make_float4(o4[0], o4[1], o4[2], o4[3]);
+                    }
                 }
             } else {
 #pragma unroll
                 for (int k = 0; k < NB; ++k) {
-                    vsh[3 * k] = B[k] * vr[0]; vsh[3 * k + 1] = B[k] * vr[1]; vsh[3 * k + 2] = B[k] * vr[2];
+                    if (ACC) {
+                        vsh[3 * k] += B[k] * vr[0]; vsh[3 * k + 1] += B[k] * vr[1]; vsh[3 * k + 2] += B[k] * vr[2];
+                    } else {
+                        vsh[3 * k] = B[k] * vr[0]; vsh[3 * k + 1] = B[k] * vr[1]; vsh[3 * k + 2] = B[k] * vr[2];
+                    }
                 }
-                for (int i = 3 * NB; i < ncoef_f; ++i) vsh[i] = 0.f;
+                if (!ACC) for (int i = 3 * NB; i < ncoef_f; ++i) vsh[i] = 0.f;
             }
             // direction gradient
             float gk[NB];
@@ -362,6 +387,8 @@ project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__
             }
             float dot = x * vdx + y * vdy + z * vdz;
             vm[0] += (vdx - x * dot) * inv; vm[1] += (vdy - y * dot) * inv; vm[2] += (vdz - z * dot) * inv;
+        } else if (ACC) {
+            vsh[0] += v_col[0]; vsh[1] += v_col[1]; vsh[2] += v_col[2];
         } else {
             vsh[0] = v_col[0]; vsh[1] = v_col[1]; vsh[2] = v_col[2];
         }
@@ -434,10 +461,23 @@ project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__
         vm[1] += R[1] * vpx + R[4] * vpy + R[7] * vpz;
         vm[2] += R[2] * vpx + R[5] * vpy + R[8] * vpz;
     }
-    v_means[3 * g] = vm[0]; v_means[3 * g + 1] = vm[1]; v_means[3 * g + 2] = vm[2];
-    reinterpret_cast<float4*>(v_quats)[g] = make_float4(vq[0], vq[1], vq[2], vq[3]);
-    v_scales[3 * g] = vs[0]; v_scales[3 * g + 1] = vs[1]; v_scales[3 * g + 2] = vs[2];
-    v_opacities[g] = vo;
+    if (RAW && vis) {  // chain through exp (scales) and sigmoid (opacity); vs[] is w.r.t. the activated scale
+        vs[0] *= expf(__ldg(scales + 3 * g)); vs[1] *= expf(__ldg(scales + 3 * g + 1)); vs[2] *= expf(__ldg(scales + 3 * g + 2));
+        const float o = 1.f / (1.f + expf(-__ldg(opacities + g)));
+        vo *= o * (1.f - o);
+    }
+    if (ACC) {
+        v_means[3 * g] += vm[0]; v_means[3 * g + 1] += vm[1]; v_means[3 * g + 2] += vm[2];
+        float4 oq = reinterpret_cast<float4*>(v_quats)[g];
+        reinterpret_cast<float4*>(v_quats)[g] = make_float4(oq.x + vq[0], oq.y + vq[1], oq.z + vq[2], oq.w + vq[3]);
+        v_scales[3 * g] += vs[0]; v_scales[3 * g + 1] += vs[1]; v_scales[3 * g + 2] += vs[2];
+        v_opacities[g] += vo;
+    } else {
+        v_means[3 * g] = vm[0]; v_means[3 * g + 1] = vm[1]; v_means[3 * g + 2] = vm[2];
+        reinterpret_cast<float4*>(v_quats)[g] = make_float4(vq[0], vq[1], vq[2], vq[3]);
+        v_scales[3 * g] = vs[0]; v_scales[3 * g + 1] = vs[1]; v_scales[3 * g + 2] = vs[2];
+        v_opacities[g] = vo;
+    }
 }
 
 // Builds the packed camera block on the device from a device-resident pose and intrinsics.
@@ -510,7 +550,7 @@ static bool sh_args_ok(int sh_coeffs, int sh_degree) {
     return sh_degree <= 3 && (sh_degree + 1) * (sh_degree + 1) <= sh_coeffs;
 }
 
-extern "C" int b200_project_sh_fwd(const float* means, const float* quats, const float* scales,
+static int project_fwd_impl(bool raw, const float* means, const float* quats, const float* scales,
                                    const float* opacities, const float* shs, int sh_coeffs, int sh_degree,
                                    int64_t N, const float* cam_host, const float* cam_dev, int width, int height,
                                    int32_t* radii, float* splats, int32_t* tiles_per_gauss, int64_t* block_sums,
@@ -531,7 +571,8 @@ extern "C" int b200_project_sh_fwd(const float* means, const float* quats, const
     cudaStream_t st = (cudaStream_t)stream;
     const int cdev = load_cam(cam_host, cam_dev, width, height, st);
     if (cdev < 0) return cdev;
-#define LAUNCH(D) project_sh_fwd_kernel<D><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid)
+#define LAUNCH(D) do { if (raw) project_sh_fwd_kernel<D, true><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid); \
+                       else project_sh_fwd_kernel<D, false><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid); } while (0)
     switch (sh_degree) {
         case 0: LAUNCH(0); break;
         case 1: LAUNCH(1); break;
@@ -544,7 +585,25 @@ extern "C" int b200_project_sh_fwd(const float* means, const float* quats, const
     return b200_check_launch("project_sh_fwd");
 }
 
-extern "C" int b200_project_sh_bwd(const float* means, const float* quats, const float* scales,
+extern "C" int b200_project_sh_fwd(const float* means, const float* quats, const float* scales, const float* opacities,
+                                   const float* shs, int sh_coeffs, int sh_degree, int64_t N, const float* cam_host,
+                                   const float* cam_dev, int width, int height, int32_t* radii, float* splats,
+                                   int32_t* tiles_per_gauss, int64_t* block_sums, uint32_t* depth_keys, int32_t* gauss_ids,
+                                   int32_t* tile_grid, void* stream) {
+    return project_fwd_impl(false, means, quats, scales, opacities, shs, sh_coeffs, sh_degree, N, cam_host, cam_dev, width,
+                            height, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, stream);
+}
+
+extern "C" int b200_project_sh_fwd_raw(const float* xyz, const float* rotation, const float* scaling, const float* opacity,
+                                       const float* features, int sh_coeffs, int sh_degree, int64_t N, const float* cam_host,
+                                       const float* cam_dev, int width, int height, int32_t* radii, float* splats,
+                                       int32_t* tiles_per_gauss, int64_t* block_sums, uint32_t* depth_keys,
+                                       int32_t* gauss_ids, int32_t* tile_grid, void* stream) {
+    return project_fwd_impl(true, xyz, rotation, scaling, opacity, features, sh_coeffs, sh_degree, N, cam_host, cam_dev, width,
+                            height, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, stream);
+}
+
+static int project_bwd_impl(int mode, const float* means, const float* quats, const float* scales,
                                    const float* opacities, const float* shs, int sh_coeffs, int sh_degree,
                                    int64_t N, const float* cam_host, const float* cam_dev, int width, int height,
                                    const int32_t* radii, const float* v_splats, float* v_means, float* v_quats, float* v_scales,
@@ -560,7 +619,10 @@ extern "C" int b200_project_sh_bwd(const float* means, const float* quats, const
     cudaStream_t st = (cudaStream_t)stream;
     const int cdev = load_cam(cam_host, cam_dev, width, height, st);
     if (cdev < 0) return cdev;
-#define LAUNCH(D) project_sh_bwd_kernel<D><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, v_splats, v_means, v_quats, v_scales, v_opacities, v_shs)
+#define ARGS means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, v_splats, v_means, v_quats, v_scales, v_opacities, v_shs
+#define LAUNCH(D) do { if (mode == 0) project_sh_bwd_kernel<D, 0><<<grid, block, 0, st>>>(ARGS); \
+                       else if (mode == 1) project_sh_bwd_kernel<D, 1><<<grid, block, 0, st>>>(ARGS); \
+                       else project_sh_bwd_kernel<D, 2><<<grid, block, 0, st>>>(ARGS); } while (0)
     switch (sh_degree) {
         case 0: LAUNCH(0); break;
         case 1: LAUNCH(1); break;
@@ -569,6 +631,25 @@ extern "C" int b200_project_sh_bwd(const float* means, const float* quats, const
         default: LAUNCH(-1); break;
     }
 #undef LAUNCH
+#undef ARGS
     cam_used(cdev, st);
     return b200_check_launch("project_sh_bwd");
+}
+
+extern "C" int b200_project_sh_bwd(const float* means, const float* quats, const float* scales, const float* opacities,
+                                   const float* shs, int sh_coeffs, int sh_degree, int64_t N, const float* cam_host,
+                                   const float* cam_dev, int width, int height, const int32_t* radii, const float* v_splats,
+                                   float* v_means, float* v_quats, float* v_scales, float* v_opacities, float* v_shs,
+                                   void* stream) {
+    return project_bwd_impl(0, means, quats, scales, opacities, shs, sh_coeffs, sh_degree, N, cam_host, cam_dev, width, height,
+                            radii, v_splats, v_means, v_quats, v_scales, v_opacities, v_shs, stream);
+}
+
+extern "C" int b200_project_sh_bwd_raw(const float* xyz, const float* rotation, const float* scaling, const float* opacity,
+                                       const float* features, int sh_coeffs, int sh_degree, int64_t N, const float* cam_host,
+                                       const float* cam_dev, int width, int height, const int32_t* radii,
+                                       const float* v_splats, float* v_xyz, float* v_rotation, float* v_scaling,
+                                       float* v_opacity, float* v_features, int accumulate, void* stream) {
+    return project_bwd_impl(accumulate ? 2 : 1, xyz, rotation, scaling, opacity, features, sh_coeffs, sh_degree, N, cam_host,
+                            cam_dev, width, height, radii, v_splats, v_xyz, v_rotation, v_scaling, v_opacity, v_features, stream);
 }

@@ -106,7 +106,7 @@ def _sort_scratch(M: int, dev) -> torch.Tensor:
 
 def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional[int], cam, width: int,
                     height: int, keep_unsorted: bool = False, method: str = "auto",
-                    with_isect_ids: bool = False) -> Dict[str, torch.Tensor]:
+                    with_isect_ids: bool = False, raw: bool = False) -> Dict[str, torch.Tensor]:
     """Stages 1-2 (projection+SH, tile binning, radix sort, tile ranges).  One host sync (reads M).
 
     method "keys64": literal gsplat formulation — emit (tile<<32|depth) int64 keys, sort M pairs.
@@ -142,8 +142,9 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
     if split:
         dkeys_a = torch.empty(max(N, 1), dtype=torch.int32, device=dev)
         gids_a = torch.empty(max(N, 1), dtype=torch.int32, device=dev)
+    project_fwd = lib.b200_project_sh_fwd_raw if raw else lib.b200_project_sh_fwd  # raw: activations fused in
     with _stage("project_sh_fwd"):
-        check(lib.b200_project_sh_fwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors),
+        check(project_fwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors),
                                       sh_coeffs, deg, N, None, _ptr(cam), width, height, _ptr(radii), _ptr(splats),
                                       _ptr(tiles_per_gauss), _ptr(block_sums),
                                       _ptr(dkeys_a) if split else None, _ptr(gids_a) if split else None,
@@ -252,14 +253,20 @@ class RasterizeSplats(torch.autograd.Function):
     @staticmethod
     @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
     def forward(ctx, means, quats, scales, opacities, colors, cam, width, height, sh_degree, chset, background,
-                with_isect_ids=False, method="auto"):
+                with_isect_ids=False, method="auto", raw=False, grad_into=None):
+        """raw=True: the five tensors are the RAW parameters (xyz, rotation, log-scaling, opacity logits,
+        features) and the activations are fused into the kernels.  grad_into = (g_xyz, g_rotation, g_scaling,
+        g_opacity, g_features): backward ADDS the raw-parameter gradients into these buffers in place (and
+        returns None for the inputs) instead of handing fresh tensors to autograd."""
         _require_cuda(means, quats, scales, opacities, colors)
         means, quats, scales = means.contiguous(), quats.contiguous(), scales.contiguous()
         opacities, colors = opacities.contiguous(), colors.contiguous()
         dev = means.device
+        if grad_into is not None and not raw:
+            raise ValueError("grad_into needs raw=True")
         with torch.cuda.device(dev):
             b = project_and_bin(means, quats, scales, opacities, colors, sh_degree, cam, width, height,
-                                method=method, with_isect_ids=with_isect_ids)
+                                method=method, with_isect_ids=with_isect_ids, raw=raw)
             if b["isect_ids"] is None:
                 b["isect_ids"] = torch.empty(0, dtype=torch.int64, device=dev)
             nch = _NCH[chset]
@@ -273,7 +280,7 @@ class RasterizeSplats(torch.autograd.Function):
                                           _ptr(last_ids), _stream()), "b200_raster_fwd")
         ctx.save_for_backward(means, quats, scales, opacities, colors, b["radii"], b["splats"], b["flatten_ids"],
                               b["isect_offsets"], alpha, last_ids)
-        ctx.cfg = (cam, width, height, sh_degree, chset, bg, n_bg, b["M"])
+        ctx.cfg = (cam, width, height, sh_degree, chset, bg, n_bg, b["M"], raw, grad_into)
         ctx.set_materialize_grads(False)  # unused outputs hand backward() None instead of freshly zero-filled tensors
         ctx.mark_non_differentiable(b["radii"], b["splats"], b["tiles_per_gauss"], b["isect_ids"],
                                     b["flatten_ids"], b["isect_offsets"], last_ids)
@@ -284,7 +291,7 @@ class RasterizeSplats(torch.autograd.Function):
     @torch.amp.custom_bwd(device_type="cuda")
     def backward(ctx, v_render, v_alpha, *_unused):
         means, quats, scales, opacities, colors, radii, splats, flatten_ids, offsets, alpha, last_ids = ctx.saved_tensors
-        cam, width, height, sh_degree, chset, bg, n_bg, M = ctx.cfg
+        cam, width, height, sh_degree, chset, bg, n_bg, M, raw, grad_into = ctx.cfg
         dev = means.device
         N = means.shape[0]
         nch = _NCH[chset]
@@ -300,26 +307,41 @@ class RasterizeSplats(torch.autograd.Function):
                 check(lib.b200_raster_bwd(_ptr(splats), _ptr(flatten_ids), _ptr(offsets), M, width, height, chset,
                                           _ptr(bg), n_bg, _ptr(alpha), _ptr(last_ids), _ptr(v_render), _ptr(v_alpha), _ptr(v_splats),
                                           st), "b200_raster_bwd")
-            v_means = torch.empty_like(means)
-            v_quats = torch.empty_like(quats)
-            v_scales = torch.empty_like(scales)
-            v_opac = torch.empty_like(opacities)
-            v_colors = torch.empty_like(colors)
             if sh_degree is None:
                 sh_coeffs, deg = 1, -1
             else:
                 sh_coeffs, deg = colors.shape[1], int(sh_degree)
+            if grad_into is not None:
+                v_means, v_quats, v_scales, v_opac, v_colors = grad_into
+                for gbuf, ref in zip(grad_into, (means, quats, scales, opacities, colors)):
+                    if gbuf.numel() != ref.numel() or not gbuf.is_contiguous() or gbuf.dtype != torch.float32:
+                        raise RuntimeError("grad_into buffers must be contiguous fp32 with the parameters' sizes")
+            else:
+                v_means = torch.empty_like(means)
+                v_quats = torch.empty_like(quats)
+                v_scales = torch.empty_like(scales)
+                v_opac = torch.empty_like(opacities)
+                v_colors = torch.empty_like(colors)
             with _stage("project_sh_bwd"):
-                check(lib.b200_project_sh_bwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors),
-                                              sh_coeffs, deg, N, None, _ptr(cam), width, height, _ptr(radii),
-                                              _ptr(v_splats),
-                                              _ptr(v_means), _ptr(v_quats), _ptr(v_scales), _ptr(v_opac),
-                                              _ptr(v_colors), st), "b200_project_sh_bwd")
-        return v_means, v_quats, v_scales, v_opac, v_colors, None, None, None, None, None, None, None, None
+                if raw:
+                    check(lib.b200_project_sh_bwd_raw(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities),
+                                                      _ptr(colors), sh_coeffs, deg, N, None, _ptr(cam), width, height,
+                                                      _ptr(radii), _ptr(v_splats), _ptr(v_means), _ptr(v_quats),
+                                                      _ptr(v_scales), _ptr(v_opac), _ptr(v_colors),
+                                                      1 if grad_into is not None else 0, st), "b200_project_sh_bwd_raw")
+                else:
+                    check(lib.b200_project_sh_bwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors),
+                                                  sh_coeffs, deg, N, None, _ptr(cam), width, height, _ptr(radii),
+                                                  _ptr(v_splats), _ptr(v_means), _ptr(v_quats), _ptr(v_scales), _ptr(v_opac),
+                                                  _ptr(v_colors), st), "b200_project_sh_bwd")
+        if grad_into is not None:
+            return (None,) * 15
+        return v_means, v_quats, v_scales, v_opac, v_colors, None, None, None, None, None, None, None, None, None, None
 
 
 def _render_one(means, quats, scales, opacities, colors, viewmat, K, width, height, sh_degree, render_mode,
-                background, near_plane, far_plane, eps2d, radius_clip, with_isect_ids=False, method="auto"):
+                background, near_plane, far_plane, eps2d, radius_clip, with_isect_ids=False, method="auto",
+                raw=False, grad_into=None):
     chset = _MODES[render_mode]
     nch = _NCH[chset]
     # the background stays on the device (no host read-back); the depth channel composites over 0
@@ -332,7 +354,7 @@ def _render_one(means, quats, scales, opacities, colors, viewmat, K, width, heig
         bg = (bgt, 3)
     cam = make_cam(viewmat, K, int(width), int(height), near_plane, far_plane, eps2d, radius_clip)
     out = RasterizeSplats.apply(means, quats, scales, opacities, colors, cam, int(width), int(height), sh_degree,
-                                chset, bg, with_isect_ids, method)
+                                chset, bg, with_isect_ids, method, raw, grad_into)
     render, alpha, radii, splats, tiles_per_gauss, isect_ids, flatten_ids, offsets, last_ids = out
     if render_mode in ("ED", "RGB+ED"):
         render = torch.cat([render[..., :-1], render[..., -1:] / alpha.clamp(min=1e-10)], dim=-1)
@@ -345,7 +367,8 @@ def rasterization(means: torch.Tensor, quats: torch.Tensor, scales: torch.Tensor
                   near_plane: float = 0.01, far_plane: float = 1e10, radius_clip: float = 0.0,
                   eps2d: float = 0.3, sh_degree: Optional[int] = None, packed: bool = False,
                   tile_size: int = 16, backgrounds: Optional[torch.Tensor] = None, render_mode: str = "RGB",
-                  meta_isect_ids: bool = False, binning: str = "auto", **unsupported) -> Tuple[torch.Tensor, torch.Tensor, Dict]:
+                  meta_isect_ids: bool = False, binning: str = "auto", raw_params: bool = False,
+                  grad_into=None, **unsupported) -> Tuple[torch.Tensor, torch.Tensor, Dict]:
     """Drop-in for ``gsplat.rasterization`` with the argument set the reference uses.
 
     means[N,3] quats[N,4](wxyz) scales[N,3] opacities[N] colors=[N,K,3] SH coefficients (``sh_degree``
@@ -354,7 +377,11 @@ def rasterization(means: torch.Tensor, quats: torch.Tensor, scales: torch.Tensor
 
     Extensions (not gsplat arguments): ``meta_isect_ids=True`` materialises the sorted int64
     ``meta["isect_ids"]`` (the fast path never needs them: the reference reads only ``means2d`` and
-    ``radii``, gsplat_backend.py:204-208); ``binning`` selects "split" / "keys64" / "auto" (project_and_bin).
+    ``radii``, gsplat_backend.py:204-208); ``binning`` selects "split" / "keys64" / "auto" (project_and_bin);
+    ``raw_params=True`` takes the RAW parameters of the reference's GaussianModel (scales = log-scaling,
+    opacities = logits, quats un-normalised, colors = features_dc ++ features_rest) and applies the getters'
+    activations inside the kernels; ``grad_into`` (raw only) accumulates the gradients into caller buffers
+    (see :class:`RasterizeSplats`, :mod:`store`).
     """
     if render_mode not in _MODES:
         raise ValueError(f"render_mode must be one of {sorted(_MODES)}, got {render_mode!r}")
@@ -375,7 +402,8 @@ def rasterization(means: torch.Tensor, quats: torch.Tensor, scales: torch.Tensor
     for c in range(Ccam):
         bg = None if backgrounds is None else (backgrounds[c] if backgrounds.dim() == 2 else backgrounds)
         r, a, m = _render_one(means, quats, scales, opacities, colors, viewmats[c], Ks[c], width, height, sh_degree,
-                              render_mode, bg, near_plane, far_plane, eps2d, radius_clip, meta_isect_ids, binning)
+                              render_mode, bg, near_plane, far_plane, eps2d, radius_clip, meta_isect_ids, binning,
+                              raw_params, grad_into)
         renders.append(r)
         alphas.append(a)
         metas.append(m)

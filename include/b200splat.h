@@ -178,6 +178,28 @@ int b200_project_sh_bwd(const float* means, const float* quats, const float* sca
                         float* v_means, float* v_quats, float* v_scales, float* v_opacities,
                         float* v_shs, void* stream);
 
+/* ---- stages 1 / 4b on the RAW parameter store ----------------------------------
+ * Same as b200_project_sh_fwd / _bwd, but the inputs are the reference's raw parameters
+ * (src/gaussians/gaussian_model.py:65-76): xyz[N,3], rotation[N,4] (un-normalised), scaling[N,3] (log),
+ * opacity[N] (logit), features[N,sh_coeffs,3] (features_dc ++ features_rest, stored contiguously by the
+ * parameter store).  The getters' activations (gaussian_model.py:90-108: exp, sigmoid, F.normalize, cat)
+ * are applied in registers, so no activated copy of the store is materialised, and the backward stage
+ * returns gradients w.r.t. the RAW parameters.  accumulate != 0: the gradients are ADDED into the
+ * caller's buffers (the flat gradient store shared by the views of a step and by the NCCL all-reduce);
+ * culled Gaussians and SH coefficients above sh_degree are then left untouched. */
+int b200_project_sh_fwd_raw(const float* xyz, const float* rotation, const float* scaling,
+                            const float* opacity, const float* features, int sh_coeffs, int sh_degree,
+                            int64_t N, const float* cam_host, const float* cam_dev, int width, int height,
+                            int32_t* radii, float* splats, int32_t* tiles_per_gauss,
+                            int64_t* block_sums, uint32_t* depth_keys, int32_t* gauss_ids,
+                            int32_t* tile_grid, void* stream);
+int b200_project_sh_bwd_raw(const float* xyz, const float* rotation, const float* scaling,
+                            const float* opacity, const float* features, int sh_coeffs, int sh_degree,
+                            int64_t N, const float* cam_host, const float* cam_dev, int width, int height,
+                            const int32_t* radii, const float* v_splats,
+                            float* v_xyz, float* v_rotation, float* v_scaling, float* v_opacity,
+                            float* v_features, int accumulate, void* stream);
+
 /* ---- stage 5: densification statistics (reference trainer.py:786-791) -------------------------
  * accum[N,3] += ||xyz_grad[n,:]||_2 (broadcast over the 3 columns); count[N] += 1. */
 int b200_densify_stats(const float* xyz_grad, int64_t N, float* accum, float* count, void* stream);
