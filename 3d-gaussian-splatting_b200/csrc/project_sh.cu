@@ -266,6 +266,51 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
 // w.r.t. the RAW parameters written.  MODE 2: raw parameters, gradients ACCUMULATED into the caller's buffers
 // (the flat gradient store): views after the first add in place, culled Gaussians and SH coefficients above
 // the active degree are not touched at all.
+//
+// The 192-B SH gradient row of a Gaussian is produced by one thread but stored by the WARP: rows are staged in
+// shared memory (two halves of six 16-B vectors, padded to 7 so that staging is conflict-free) and written —
+// or, in MODE 2, read-modified-written with all loads of a half issued back to back — as runs of 96 contiguous
+// bytes by consecutive lanes.  A per-thread "+=" over its own row would serialise twelve dependent round trips.
+template <int NB, bool ACC>
+__device__ __forceinline__ void store_sh_rows(float4* __restrict__ s_buf, const float* Bk, const float* vr, unsigned vis_mask,
+                                              int lane, int64_t g0, int64_t N, float* __restrict__ v_shs) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+            float o4[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int e = 4 * (6 * h + i) + j, k = e / 3, ch = e - 3 * k;
+                o4[j] = (k < NB) ? Bk[k < NB ? k : 0] * vr[ch] : 0.f;
+            }
+            s_buf[lane * 7 + i] = make_float4(o4[0], o4[1], o4[2], o4[3]);
+        }
+        __syncwarp();
+        float4* out[6];
+        float4 old[6];
+        bool on[6];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+            const int f = j * 32 + lane, r = f / 6, c = f - 6 * r;
+            const int64_t gg = g0 + r;
+            on[j] = gg < N && (!ACC || (((vis_mask >> r) & 1u) && 4 * (6 * h + c) < 3 * NB));
+            out[j] = reinterpret_cast<float4*>(v_shs) + gg * 12 + 6 * h + c;
+            if (ACC && on[j]) old[j] = *out[j];
+        }
+#pragma unroll
+        for (int j = 0; j < 6; ++j) {
+            const int f = j * 32 + lane, r = f / 6, c = f - 6 * r;
+            if (on[j]) {
+                float4 v = s_buf[r * 7 + c];
+                if (ACC) { v.x += old[j].x; v.y += old[j].y; v.z += old[j].z; v.w += old[j].w; }
+                *out[j] = v;
+            }
+        }
+        __syncwarp();
+    }
+}
+
 template <int DEG, int MODE>
 __global__ void __launch_bounds__(PROJ_THREADS, 2)
 project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__ quats,
@@ -275,81 +320,50 @@ project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__
                       float* __restrict__ v_means, float* __restrict__ v_quats, float* __restrict__ v_scales,
                       float* __restrict__ v_opacities, float* __restrict__ v_shs) {
     const Cam& cam = c_cam;
-    int64_t g = (int64_t)blockIdx.x * PROJ_THREADS + threadIdx.x;
-    if (g >= N) return;
-    int2 rad = __ldg(reinterpret_cast<const int2*>(radii) + g);
-    bool vis = rad.x > 0 && rad.y > 0;
+    constexpr bool RAW = MODE != 0, ACC = MODE == 2;
+    constexpr int D = DEG < 0 ? 0 : DEG;
+    constexpr int NB = ShCount<D>::NB;
+    __shared__ float4 s_sh[PROJ_THREADS / 32][32 * 7];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int64_t g = (int64_t)blockIdx.x * PROJ_THREADS + threadIdx.x;
+    const bool in = g < N;
+    bool vis = false;
+    if (in) {
+        const int2 rad = __ldg(reinterpret_cast<const int2*>(radii) + g);
+        vis = rad.x > 0 && rad.y > 0;
+    }
+    const bool coop = DEG >= 0 && vec_ok && sh_coeffs == 16;  // block-uniform
     float vm[3] = {0.f, 0.f, 0.f}, vq[4] = {0.f, 0.f, 0.f, 0.f}, vs[3] = {0.f, 0.f, 0.f}, vo = 0.f;
     const int ncoef_f = sh_coeffs * 3;
     float* vsh = (DEG >= 0) ? v_shs + g * (int64_t)ncoef_f : v_shs + 3 * g;
-    constexpr bool RAW = MODE != 0, ACC = MODE == 2;
+    float px = 0.f, py = 0.f, pz = 0.f;
+    float4 g0 = make_float4(0.f, 0.f, 0.f, 0.f), g1 = g0, g2 = g0;
+    float B[NB], vr[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+    for (int k = 0; k < NB; ++k) B[k] = 0.f;
 
-    if (!vis) {
-        if (ACC) return;
-        if (DEG >= 0) {
-            if (vec_ok) {
-                float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                for (int i = 0; i < ncoef_f / 4; ++i) reinterpret_cast<float4*>(vsh)[i] = z4;
-            } else {
-                for (int i = 0; i < ncoef_f; ++i) vsh[i] = 0.f;
-            }
-        } else {
-            vsh[0] = vsh[1] = vsh[2] = 0.f;
-        }
-    } else {
-        float px = __ldg(means + 3 * g), py = __ldg(means + 3 * g + 1), pz = __ldg(means + 3 * g + 2);
-        float4 q = __ldg(reinterpret_cast<const float4*>(quats) + g);
-        float sx = __ldg(scales + 3 * g), sy = __ldg(scales + 3 * g + 1), sz = __ldg(scales + 3 * g + 2);
-        if (RAW) { sx = expf(sx); sy = expf(sy); sz = expf(sz); }
+    // ---- phase 1: SH colour VJP (A.2) ----
+    if (vis) {
+        px = __ldg(means + 3 * g); py = __ldg(means + 3 * g + 1); pz = __ldg(means + 3 * g + 2);
         const float4* vrec = reinterpret_cast<const float4*>(v_splats) + 3 * g;
-        float4 g0 = __ldg(vrec), g1 = __ldg(vrec + 1), g2 = __ldg(vrec + 2);
-        float v_mx = g0.x, v_my = g0.y, v_A = g0.z, v_B = g0.w, v_C = g1.x;
-        vo = g1.y;
-        float v_col[3] = {g1.z, g1.w, g2.x};
-        float v_depth = g2.y;
-        Proj P;
-        project_core(cam, px, py, pz, q, sx, sy, sz, P);
-
-        // ---- SH colour VJP (A.2) ----
+        g0 = __ldg(vrec); g1 = __ldg(vrec + 1); g2 = __ldg(vrec + 2);
+        const float v_col[3] = {g1.z, g1.w, g2.x};
         if (DEG >= 0) {
-            constexpr int D = DEG < 0 ? 0 : DEG;
-            constexpr int NB = ShCount<D>::NB;
             float c[ShCount<D>::NV * 4];
             load_sh<D>(shs, g, sh_coeffs, vec_ok, c);
             float ux = px - cam.campos[0], uy = py - cam.campos[1], uz = pz - cam.campos[2];
             float inv = rsqrtf(ux * ux + uy * uy + uz * uz);
             float x = ux * inv, y = uy * inv, z = uz * inv;
-            float B[NB];
             sh_basis<D>(x, y, z, B);
             float rgb[3] = {0.f, 0.f, 0.f};
 #pragma unroll
             for (int k = 0; k < NB; ++k) {
                 rgb[0] += B[k] * c[3 * k]; rgb[1] += B[k] * c[3 * k + 1]; rgb[2] += B[k] * c[3 * k + 2];
             }
-            float vr[3];
 #pragma unroll
             for (int ch = 0; ch < 3; ++ch) vr[ch] = (rgb[ch] + 0.5f >= 0.f) ? v_col[ch] : 0.f;
             // coefficient gradients: v_c[k][ch] = B_k * v_rgb[ch], zero above the active degree
-            if (vec_ok && sh_coeffs == 16) {
-#pragma unroll
-                for (int i = 0; i < 12; ++i) {
-                    float o4[4];
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        constexpr int dummy = 0; (void)dummy;
-                        const int e = 4 * i + j, k = e / 3, ch = e - 3 * k;
-                        o4[j] = (k < NB) ? B[k < NB ? k : 0] * vr[ch] : 0.f;
-                    }
-                    if (ACC) {
-                        if (4 * i < 3 * NB) {
-                            float4 old = reinterpret_cast<float4*>(vsh)[i];
-                            reinterpret_cast<float4*>(vsh)[i] = make_float4(old.x + o4[0], old.y + o4[1], old.z + o4[2], old.w + o4[3]);
-                        }
-                    } else {
-                        reinterpret_cast<float4*>(vsh)[i] = make_float4(o4[0], o4[1], o4[2], o4[3]);
-                    }
-                }
-            } else {
+            if (!coop) {
 #pragma unroll
                 for (int k = 0; k < NB; ++k) {
                     if (ACC) {
@@ -392,7 +406,27 @@ project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__
         } else {
             vsh[0] = v_col[0]; vsh[1] = v_col[1]; vsh[2] = v_col[2];
         }
+    } else if (in && !ACC && !(DEG >= 0 && coop)) {
+        const int nz = (DEG >= 0) ? ncoef_f : 3;
+        for (int i = 0; i < nz; ++i) vsh[i] = 0.f;
+    }
+    if (DEG >= 0 && coop) {
+        const unsigned vis_mask = __ballot_sync(0xffffffffu, vis);
+        if (!ACC || vis_mask)
+            store_sh_rows<NB, ACC>(s_sh[wid], B, vr, vis_mask, lane, g - lane, N, v_shs);
+    }
+    if (!in || (ACC && !vis)) return;
 
+    // ---- phase 2: projection VJP ----
+    if (vis) {
+        float4 q = __ldg(reinterpret_cast<const float4*>(quats) + g);
+        float sx = __ldg(scales + 3 * g), sy = __ldg(scales + 3 * g + 1), sz = __ldg(scales + 3 * g + 2);
+        if (RAW) { sx = expf(sx); sy = expf(sy); sz = expf(sz); }
+        float v_mx = g0.x, v_my = g0.y, v_A = g0.z, v_B = g0.w, v_C = g1.x;
+        vo = g1.y;
+        float v_depth = g2.y;
+        Proj P;
+        project_core(cam, px, py, pz, q, sx, sy, sz, P);
         // ---- conic -> 2-D covariance (A.6) ----
         float inv_det = 1.f / P.det;
         float A = P.c * inv_det, Bc = -P.b * inv_det, C = P.a * inv_det;
@@ -460,18 +494,21 @@ project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__
         vm[0] += R[0] * vpx + R[3] * vpy + R[6] * vpz;
         vm[1] += R[1] * vpx + R[4] * vpy + R[7] * vpz;
         vm[2] += R[2] * vpx + R[5] * vpy + R[8] * vpz;
+        if (RAW) {  // chain through exp (scales) and sigmoid (opacity); vs[] was w.r.t. the activated scale
+            vs[0] *= sx; vs[1] *= sy; vs[2] *= sz;
+            const float o = 1.f / (1.f + expf(-__ldg(opacities + g)));
+            vo *= o * (1.f - o);
+        }
     }
-    if (RAW && vis) {  // chain through exp (scales) and sigmoid (opacity); vs[] is w.r.t. the activated scale
-        vs[0] *= expf(__ldg(scales + 3 * g)); vs[1] *= expf(__ldg(scales + 3 * g + 1)); vs[2] *= expf(__ldg(scales + 3 * g + 2));
-        const float o = 1.f / (1.f + expf(-__ldg(opacities + g)));
-        vo *= o * (1.f - o);
-    }
-    if (ACC) {
-        v_means[3 * g] += vm[0]; v_means[3 * g + 1] += vm[1]; v_means[3 * g + 2] += vm[2];
-        float4 oq = reinterpret_cast<float4*>(v_quats)[g];
+    if (ACC) {  // all loads first: one round trip instead of eleven dependent ones
+        const float m0 = v_means[3 * g], m1 = v_means[3 * g + 1], m2 = v_means[3 * g + 2];
+        const float4 oq = reinterpret_cast<float4*>(v_quats)[g];
+        const float s0 = v_scales[3 * g], s1 = v_scales[3 * g + 1], s2 = v_scales[3 * g + 2];
+        const float o0 = v_opacities[g];
+        v_means[3 * g] = m0 + vm[0]; v_means[3 * g + 1] = m1 + vm[1]; v_means[3 * g + 2] = m2 + vm[2];
         reinterpret_cast<float4*>(v_quats)[g] = make_float4(oq.x + vq[0], oq.y + vq[1], oq.z + vq[2], oq.w + vq[3]);
-        v_scales[3 * g] += vs[0]; v_scales[3 * g + 1] += vs[1]; v_scales[3 * g + 2] += vs[2];
-        v_opacities[g] += vo;
+        v_scales[3 * g] = s0 + vs[0]; v_scales[3 * g + 1] = s1 + vs[1]; v_scales[3 * g + 2] = s2 + vs[2];
+        v_opacities[g] = o0 + vo;
     } else {
         v_means[3 * g] = vm[0]; v_means[3 * g + 1] = vm[1]; v_means[3 * g + 2] = vm[2];
         reinterpret_cast<float4*>(v_quats)[g] = make_float4(vq[0], vq[1], vq[2], vq[3]);

@@ -269,6 +269,21 @@ def run_b200(args):
             flat = pkg.allreduce_gradients(params_list, world * V, flat=flat)
         return float(tot.item())  # D2H read of the step's result
 
+    # f1: the same step from the RAW parameter store — activations fused into the kernels, gradients
+    # accumulated in-kernel into the flat buffer that the all-reduce then takes as is
+    store = pkg.GaussianStore.from_tensors(sc["xyz"].to(dev), sc["features_dc"].to(dev), sc["features_rest"].to(dev),
+                                           sc["scaling"].to(dev), sc["rotation"].to(dev), sc["opacity"].to(dev))
+
+    def step_store(step):
+        store.zero_grad()
+        for v in range(V):
+            vp = {"world_view_transform": poses_dev[view_index(step, v)], "image_width": W, "image_height": H}
+            res = store.render(K, vp, bg_color=bg, render_mode="RGB", sh_degree=deg)
+            res["render"].backward(v_render)
+        if world > 1:
+            dist.all_reduce(store.flat_grad)
+            store.flat_grad.mul_(1.0 / (world * V))
+
     def timed(fn, steps, warmup, timer=None):
         for i in range(warmup):
             fn(i)
@@ -304,6 +319,7 @@ def run_b200(args):
         sampler.start()
     ms_dev, launches = timed(step_device, args.steps, args.warmup, timer)
     ms_e2e, _ = timed(step_e2e, args.steps, max(1, args.warmup // 2))
+    ms_store, _ = timed(step_store, args.steps, max(1, args.warmup // 2))
     if rank == 0:
         sampler.stop_flag.set()
         sampler.join(timeout=2)
@@ -392,6 +408,10 @@ def run_b200(args):
         # rank per step (the reference's batch_size, training_config.py:55); rasterizer fwd+bwd (+ all-reduce) only
         "train_it_per_s": {"device": 1e3 / (ms_dev / args.steps), "e2e": 1e3 / (ms_e2e / args.steps),
                            "views_per_step": world * V},
+        "f1_store_path": {"value": pix_per_step / (ms_store / args.steps / 1e3) / 1e6, "unit": "Mpix/s",
+                          "ms_per_step": ms_store / args.steps,
+                          "what": "same step from GaussianStore (raw parameters, fused activations, in-kernel gradient "
+                                  "accumulation into the flat buffer); not the drop-in call, reported beside it"},
         "clocks": sampler.summary(),
         "roofline": roofline,
         "cpu_baseline": cpu_baseline,

@@ -16,7 +16,16 @@ be = pkg.B200Backend(sc["K"].to(dev))
 v = torch.randn(H, W, 3, generator=torch.Generator().manual_seed(1)).to(dev)
 vp = {"world_view_transform": sc["viewmat"].to(dev), "image_width": W, "image_height": H}
 bg = torch.zeros(3, device=dev)
+mode = sys.argv[2] if len(sys.argv) > 2 else "backend"
+store = pkg.GaussianStore.from_tensors(*[sc[k].to(dev) for k in ("xyz", "features_dc", "features_rest", "scaling", "rotation", "opacity")])
+Kd = sc["K"].to(dev)
 def step():
+    if mode == "store":
+        store.zero_grad()
+        for _ in range(4):
+            res = store.render(Kd, vp, bg_color=bg, render_mode="RGB", sh_degree=deg)
+            res["render"].backward(v)
+        return
     for p in leaves.values(): p.grad = None
     for _ in range(4):
         res = be.render_with_depth(leaves, vp, bg_color=bg, render_mode="RGB", device="cuda", sh_degree=deg)
@@ -31,10 +40,15 @@ ev.sort(key=lambda e: e.time_range.start)
 t0, t1 = ev[0].time_range.start, max(e.time_range.end for e in ev)
 busy = sum(e.time_range.end - e.time_range.start for e in ev)
 print(f"span {(t1-t0)/1e3:.3f} ms, busy {busy/1e3:.3f} ms, idle {(t1-t0-busy)/1e3:.3f} ms, kernels {len(ev)}  (8 views)")
+agg = {}
+for e in ev:
+    a = agg.setdefault(e.name[:60], [0, 0.0]); a[0] += 1; a[1] += e.time_range.end - e.time_range.start
+for k, (n, t) in sorted(agg.items(), key=lambda x: -x[1][1])[:14]:
+    print(f"{t/n:9.1f} us x{n:3d}  {k}")
 gaps = {}
 for a, b in zip(ev, ev[1:]):
     g = b.time_range.start - a.time_range.end
     k = (a.name[:40], b.name[:40])
     s = gaps.setdefault(k, [0, 0.0]); s[0] += 1; s[1] += max(g, 0)
-for k, (n, g) in sorted(gaps.items(), key=lambda x: -x[1][1])[:25]:
+for k, (n, g) in sorted(gaps.items(), key=lambda x: -x[1][1])[:8]:
     print(f"{g/n:8.1f} us x{n:3d}  after {k[0]:40s} before {k[1]}")
