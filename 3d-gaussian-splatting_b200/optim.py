@@ -1,0 +1,56 @@
+"""StoreAdam — the reference's optimiser (``Adam(params, lr=0.0, eps=1e-15)`` over six parameter groups,
+src/training/trainer.py:331-340) as one kernel over the flat GaussianStore buffers.
+
+``lrs`` uses the reference's group names (``xyz, f_dc, f_rest, opacity, scaling, rotation``; the store's attribute
+names ``features_dc`` / ``features_rest`` are accepted too) and stays mutable, so the trainer's per-iteration
+position-rate schedule (``_update_learning_rate``, trainer.py:373-383) is ``opt.lrs["xyz"] = lr``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Tuple
+
+import torch
+
+from ._lib import lib, check
+
+_ALIASES = {"features_dc": "f_dc", "features_rest": "f_rest"}
+
+
+class StoreAdam:
+    def __init__(self, store, lrs: Dict[str, float], betas: Tuple[float, float] = (0.9, 0.999), eps: float = 1e-15):
+        self.store = store
+        self.lrs = {_ALIASES.get(k, k): float(v) for k, v in lrs.items()}
+        missing = {"xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation"} - set(self.lrs)
+        if missing:
+            raise ValueError(f"StoreAdam: missing learning rates for {sorted(missing)}")
+        self.betas, self.eps = (float(betas[0]), float(betas[1])), float(eps)
+        self.exp_avg = torch.zeros_like(store.flat)
+        self.exp_avg_sq = torch.zeros_like(store.flat)
+        self.t = 0
+
+    def _segments(self):
+        st, n = self.store, len(self.store)
+        o = st._offsets
+        rows = [
+            (o["xyz"], o["xyz"] + 3 * n, self.lrs["xyz"], 0.0, 0, 0),
+            (o["scaling"], o["scaling"] + 3 * n, self.lrs["scaling"], 0.0, 0, 0),
+            (o["rotation"], o["rotation"] + 4 * n, self.lrs["rotation"], 0.0, 0, 0),
+            (o["opacity"], o["opacity"] + n, self.lrs["opacity"], 0.0, 0, 0),
+            (o["features"], o["features"] + 48 * n, self.lrs["f_dc"], self.lrs["f_rest"], 48, 3),
+        ]
+        flat = [float(x) for r in rows for x in r]
+        return (C.c_double * len(flat))(*flat), len(rows)
+
+    @torch.no_grad()
+    def step(self) -> None:
+        st = self.store
+        self.t += 1
+        segs, n_seg = self._segments()
+        with torch.cuda.device(st.flat.device):
+            check(lib.b200_adam_step(st.flat.data_ptr(), st.flat_grad.data_ptr(), self.exp_avg.data_ptr(),
+                                     self.exp_avg_sq.data_ptr(), st.flat.numel(), segs, n_seg, self.t, self.betas[0],
+                                     self.betas[1], self.eps, torch.cuda.current_stream().cuda_stream), "b200_adam_step")
+
+    def zero_grad(self, set_to_none: bool = False) -> None:
+        self.store.zero_grad()

@@ -212,6 +212,16 @@ int b200_densify_stats(const float* xyz_grad, int64_t N, float* accum, float* co
 int b200_l1_ssim_fwd_bwd(const float* render, const float* gt, int width, int height,
                          float lambda_dssim, float grad_scale, float* v_render, float* sums, void* stream);
 
+/* ---- f4: the optimiser step over the flat parameter store -----------------------
+ * torch.optim.Adam semantics (trainer.py:331-340: six groups, eps 1e-15; no amsgrad / weight decay) in one
+ * pass over params / grads / exp_avg / exp_avg_sq of identical flat layout (n_floats, multiple of 4, 16-B
+ * aligned).  seg_host: n_seg (<= 8) rows of six doubles {begin, end, lr, lr_alt, period, split}: elements
+ * [begin,end) use lr, except where period > 0 and (i - begin) % period >= split, which use lr_alt (the
+ * features_dc / features_rest rates inside the [N,16,3] SH block: period 48, split 3).  step = Adam's t >= 1. */
+int b200_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n_floats,
+                   const double* seg_host, int n_seg, int step, float beta1, float beta2, float eps,
+                   void* stream);
+
 #ifdef __cplusplus
 }
 #endif
