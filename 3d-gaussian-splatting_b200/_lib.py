@@ -53,6 +53,7 @@ SIGNATURES = {
     "b200_project_sh_bwd_raw": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _i, _p]),
     "b200_l1_ssim_fwd_bwd": (_i, [_p, _p, _i, _i, C.c_float, C.c_float, _p, _p, _p]),
     "b200_adam_step": (_i, [_p, _p, _p, _p, _l, _p, _i, _i, C.c_float, C.c_float, C.c_float, _p]),
+    "b200_store_gather": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _l, _p]),
     "b200_densify_stats": (_i, [_p, _l, _p, _p, _p]),
 }
 

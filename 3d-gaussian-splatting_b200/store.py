@@ -202,3 +202,107 @@ class GaussianStore(nn.Module):
             result["render"] = out[..., :3]
             result["accumulated_depth" if render_mode == "RGB+D" else "expected_depth"] = out[..., 3]
         return result
+
+    # ------------------------------------------------------------------ densification
+    def _layout_array(self):
+        import ctypes as C
+        o = self._offsets
+        return (C.c_int64 * 5)(o["xyz"], o["scaling"], o["rotation"], o["opacity"], o["features"])
+
+    @torch.no_grad()
+    def _rebuild(self, src_rows: torch.Tensor, keep_state: torch.Tensor, optimizer=None) -> None:
+        """New population: row j <- old row src_rows[j]; optimiser moments follow when keep_state[j] (else zero)."""
+        from ._lib import lib, check
+        dev = self.flat.device
+        old_flat, old_layout = self.flat, self._layout_array()
+        old_radii = self.max_radii_2D
+        n_new = int(src_rows.numel())
+        m_old = v_old = None
+        if optimizer is not None:
+            m_old, v_old = optimizer.exp_avg, optimizer.exp_avg_sq
+        self._allocate(n_new, dev)  # fresh flat / flat_grad, parameters re-created as views
+        m_new = torch.zeros_like(self.flat) if optimizer is not None else None
+        v_new = torch.zeros_like(self.flat) if optimizer is not None else None
+        src_rows = src_rows.to(torch.int64).contiguous()
+        ks = keep_state.to(torch.uint8).contiguous()
+        ptr = lambda t: None if t is None else t.data_ptr()  # noqa: E731
+        with torch.cuda.device(dev):
+            check(lib.b200_store_gather(old_flat.data_ptr(), ptr(m_old), ptr(v_old), old_layout, self.flat.data_ptr(),
+                                        ptr(m_new), ptr(v_new), self._layout_array(), src_rows.data_ptr(), ks.data_ptr(),
+                                        n_new, torch.cuda.current_stream().cuda_stream), "b200_store_gather")
+        if optimizer is not None:
+            optimizer.exp_avg, optimizer.exp_avg_sq = m_new, v_new
+        self.max_radii_2D = torch.where(keep_state.bool(), old_radii[src_rows], torch.zeros((), device=dev))
+        self.xyz_gradient_accum = torch.zeros(n_new, 3, device=dev)
+        self.xyz_gradient_count = torch.zeros(n_new, 1, device=dev)
+
+    @torch.no_grad()
+    def densify_and_prune(self, grads_threshold: float, min_opacity: float, extent: float, max_screen_size: float = None,
+                          optimizer=None, clone_extent_ratio: float = 0.1, prune_extent_ratio: float = 2.0,
+                          max_gaussians: int = None) -> Dict:
+        """gaussian_model.py:110-231 — same arguments, same statistics dict, same resulting population (row order,
+        values, spliced Adam moments; the split noise is drawn with the same ``torch.randn_like`` call), but the
+        population change is ONE gather over the flat buffers (``b200_store_gather``) instead of a chain of
+        ``torch.cat`` / mask copies per attribute and per optimiser buffer.  ``optimizer``: a :class:`StoreAdam`."""
+        n0 = self._n
+        dev = self.flat.device
+        stats = {"cloned": 0, "split": 0, "pruned": 0, "n_before": n0, "capped": False}
+        grads = self.xyz_gradient_accum / (self.xyz_gradient_count + 1e-8)
+        grads_norm = torch.norm(grads, dim=-1)
+        max_scale = self.get_scaling.amax(dim=-1)
+        opacity = self.get_opacity.reshape(-1)
+        hot = (grads_norm >= grads_threshold) & (opacity > min_opacity)
+        clone_mask = hot & (max_scale <= extent * clone_extent_ratio)
+        split_mask = hot & (max_scale > extent * clone_extent_ratio)
+        if max_gaussians is not None and n0 >= int(max_gaussians):
+            clone_mask = torch.zeros_like(clone_mask)
+            split_mask = torch.zeros_like(split_mask)
+            stats["capped"] = True
+        elif max_gaussians is not None:
+            n_allowed = int(max_gaussians) - n0
+            if int(clone_mask.sum().item()) + int(split_mask.sum().item()) > n_allowed:
+                stats["capped"] = True
+                combined = clone_mask | split_mask
+                keep = torch.zeros_like(combined)
+                if n_allowed > 0:  # _top_k_mask_by_grad (gaussian_model.py:233-249)
+                    idx = combined.nonzero(as_tuple=False).view(-1)
+                    keep[idx[torch.topk(grads_norm[idx], k=n_allowed).indices]] = True
+                clone_mask, split_mask = clone_mask & keep, split_mask & keep
+        clone_idx = clone_mask.nonzero(as_tuple=False).view(-1)
+        split_idx = split_mask.nonzero(as_tuple=False).view(-1)
+        keep_idx = (~split_mask).nonzero(as_tuple=False).view(-1)
+        n_k, n_c, n_s = int(keep_idx.numel()), int(clone_idx.numel()), int(split_idx.numel())
+        stats["cloned"], stats["split"] = n_c, n_s
+        # population after clone + split: [originals minus the split ones | clones | 2 x children]
+        src = torch.cat([keep_idx, clone_idx, split_idx, split_idx])
+        state = torch.cat([torch.ones(n_k, dtype=torch.bool, device=dev), torch.zeros(n_c + 2 * n_s, dtype=torch.bool, device=dev)])
+        scale_all = max_scale[src]
+        child_xyz = child_scaling = None
+        if n_s > 0:  # _split_gaussians (gaussian_model.py:278-312), same arithmetic and the same randn call
+            child_scaling = self.scaling[split_idx].repeat(2, 1) - torch.log(torch.tensor(1.6, device=dev))
+            scales = torch.exp(child_scaling)
+            xyz_rep = self.xyz[split_idx].repeat(2, 1)
+            child_xyz = xyz_rep + torch.randn_like(xyz_rep) * scales[:, :3]
+            scale_all = torch.cat([scale_all[: n_k + n_c], scales.amax(dim=-1)])
+        low_op = opacity[src] < min_opacity
+        too_big = scale_all > extent * prune_extent_ratio
+        prune = low_op | too_big
+        n_pruned = int(prune.sum().item())
+        stats["pruned"] = n_pruned
+        stats["pruned_low_op"] = int(low_op.sum().item()) if n_pruned else 0
+        stats["pruned_too_big"] = int(too_big.sum().item()) if n_pruned else 0
+        sel = (~prune).nonzero(as_tuple=False).view(-1)
+        if n_c == 0 and n_s == 0 and n_pruned == 0:
+            self.xyz_gradient_accum.zero_()
+            self.xyz_gradient_count.zero_()
+            stats["n_after"] = n0
+            return stats
+        self._rebuild(src[sel], state[sel], optimizer)
+        if n_s > 0:  # children: position in the new population, index into the child arrays
+            is_child = sel >= (n_k + n_c)
+            pos = is_child.nonzero(as_tuple=False).view(-1)
+            child = sel[pos] - (n_k + n_c)
+            self.xyz.data[pos] = child_xyz[child]
+            self.scaling.data[pos] = child_scaling[child]
+        stats["n_after"] = self._n
+        return stats

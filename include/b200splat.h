@@ -222,6 +222,17 @@ int b200_adam_step(float* params, const float* grads, float* exp_avg, float* exp
                    const double* seg_host, int n_seg, int step, float beta1, float beta2, float eps,
                    void* stream);
 
+/* ---- f2: population change of the flat store in one gather -----------------------
+ * Data movement of gaussian_model.py:110-366 (clone / split / prune with the Adam moments spliced,
+ * _replace_param_in_optimizer :9-50): destination row j of the new store is source row src_row[j]; its
+ * moments are copied when keep_state[j] != 0 (or keep_state == NULL) and zeroed otherwise.  layout_*_host:
+ * five int64 block offsets {xyz, scaling, rotation, opacity, features} of the flat buffers, in floats.
+ * The three moment pointers are all NULL or all set. */
+int b200_store_gather(const float* params_src, const float* exp_avg_src, const float* exp_avg_sq_src,
+                      const int64_t* layout_src_host, float* params_dst, float* exp_avg_dst,
+                      float* exp_avg_sq_dst, const int64_t* layout_dst_host, const int64_t* src_row,
+                      const uint8_t* keep_state, int64_t n_dst, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,138 @@
+"""SURVEY.md §8 f2 — GaussianStore.densify_and_prune against a plain-tensor restatement of the reference's
+densify_and_prune / _clone_gaussians / _split_gaussians / _prune_gaussians / densify with Adam-state splicing
+(src/gaussians/gaussian_model.py:9-50,110-366).  Same inputs and the same CUDA RNG state => identical population."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+ATTRS = ("xyz", "features_dc", "features_rest", "opacity", "scaling", "rotation")
+
+
+class RefModel:
+    """The reference's bookkeeping on plain tensors: params, Adam moments (exp_avg, exp_avg_sq) and buffers."""
+
+    def __init__(self, params, m, v, accum, count):
+        self.p, self.m, self.v = dict(params), dict(m), dict(v)
+        self.accum, self.count = accum, count
+
+    def _prune(self, keep):
+        for a in ATTRS:
+            self.p[a], self.m[a], self.v[a] = self.p[a][keep], self.m[a][keep], self.v[a][keep]
+        self.accum, self.count = self.accum[keep], self.count[keep]
+
+    def _append(self, new):
+        n_new = new["xyz"].shape[0]
+        for a in ATTRS:
+            self.p[a] = torch.cat([self.p[a], new[a]], 0)
+            self.m[a] = torch.cat([self.m[a], torch.zeros_like(new[a])], 0)
+            self.v[a] = torch.cat([self.v[a], torch.zeros_like(new[a])], 0)
+        self.accum = torch.cat([self.accum, torch.zeros(n_new, 3, device=DEV)])
+        self.count = torch.cat([self.count, torch.zeros(n_new, 1, device=DEV)])
+
+    def densify_and_prune(self, thr, min_opacity, extent, clone_ratio=0.1, prune_ratio=2.0, max_gaussians=None):
+        n_before = self.p["xyz"].shape[0]
+        grads_norm = torch.norm(self.accum / (self.count + 1e-8), dim=-1)
+        max_scale = torch.exp(self.p["scaling"]).amax(-1)
+        opacity = torch.sigmoid(self.p["opacity"]).squeeze(-1)
+        clone = (grads_norm >= thr) & (max_scale <= extent * clone_ratio) & (opacity > min_opacity)
+        split = (grads_norm >= thr) & (max_scale > extent * clone_ratio) & (opacity > min_opacity)
+        if max_gaussians is not None and n_before >= max_gaussians:
+            clone, split = torch.zeros_like(clone), torch.zeros_like(split)
+        elif max_gaussians is not None:
+            allowed = max_gaussians - n_before
+            if int(clone.sum()) + int(split.sum()) > allowed:
+                comb = clone | split
+                keep = torch.zeros_like(comb)
+                if allowed > 0:
+                    idx = comb.nonzero().view(-1)
+                    keep[idx[torch.topk(grads_norm[idx], k=allowed).indices]] = True
+                clone, split = clone & keep, split & keep
+        if clone.sum() > 0:
+            idx = clone.nonzero().view(-1)
+            self._append({a: self.p[a][idx] for a in ATTRS})
+        n_now = self.p["xyz"].shape[0]
+        if split.shape[0] < n_now:
+            split = torch.cat([split, torch.zeros(n_now - split.shape[0], dtype=torch.bool, device=DEV)])
+        if split.sum() > 0:
+            idx = split.nonzero().view(-1)
+            xyz = self.p["xyz"][idx]
+            new = {a: self.p[a][idx].repeat(2, *([1] * (self.p[a].dim() - 1))) for a in ATTRS if a != "xyz"}
+            new["scaling"] = new["scaling"] - torch.log(torch.tensor(1.6, device=DEV))
+            scales = torch.exp(new["scaling"])
+            new["xyz"] = xyz.repeat(2, 1) + torch.randn_like(xyz.repeat(2, 1)) * scales[:, :3]
+            keep = torch.ones(n_now, dtype=torch.bool, device=DEV)
+            keep[idx] = False
+            self._prune(keep)
+            self._append(new)
+        max_scale = torch.exp(self.p["scaling"]).amax(-1)
+        opacity = torch.sigmoid(self.p["opacity"]).squeeze(-1)
+        prune = (opacity < min_opacity) | (max_scale > extent * prune_ratio)
+        if prune.sum() > 0:
+            self._prune(~prune)
+        self.accum, self.count = torch.zeros_like(self.accum), torch.zeros_like(self.count)
+        return {"cloned": int(clone.sum()), "split": int(split.sum()), "pruned": int(prune.sum()),
+                "n_after": self.p["xyz"].shape[0]}
+
+
+def _setup(pkg, oracle, N, seed):
+    sc = oracle.synthetic_scene(N, 320, 200, seed=seed)
+    raw = {a: sc[a].to(DEV).clone() for a in ATTRS}
+    st = pkg.GaussianStore.from_tensors(raw["xyz"], raw["features_dc"], raw["features_rest"], raw["scaling"],
+                                        raw["rotation"], raw["opacity"])
+    lrs = {"xyz": 1.6e-4, "f_dc": 0.0025, "f_rest": 1.25e-4, "opacity": 0.05, "scaling": 0.005, "rotation": 0.001}
+    opt = pkg.StoreAdam(st, lrs)
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    opt.exp_avg.copy_(torch.randn(opt.exp_avg.shape, generator=g, device=DEV))
+    opt.exp_avg_sq.copy_(torch.rand(opt.exp_avg_sq.shape, generator=g, device=DEV))
+
+    def views(buf):  # moment buffers in the reference's per-attribute form
+        o = st._offsets
+        f = buf[o["features"]: o["features"] + 48 * N].view(N, 16, 3)
+        return {"xyz": buf[o["xyz"]: o["xyz"] + 3 * N].view(N, 3).clone(), "scaling": buf[o["scaling"]: o["scaling"] + 3 * N].view(N, 3).clone(),
+                "rotation": buf[o["rotation"]: o["rotation"] + 4 * N].view(N, 4).clone(),
+                "opacity": buf[o["opacity"]: o["opacity"] + N].view(N, 1).clone(),
+                "features_dc": f[:, 0:1].clone(), "features_rest": f[:, 1:].clone()}
+
+    accum = torch.rand(N, 3, generator=g, device=DEV) * 4e-4
+    count = torch.randint(0, 5, (N, 1), generator=g, device=DEV).float()
+    st.xyz_gradient_accum.copy_(accum)
+    st.xyz_gradient_count.copy_(count)
+    ref = RefModel(raw, views(opt.exp_avg), views(opt.exp_avg_sq), accum.clone(), count.clone())
+    return st, opt, ref
+
+
+def _moments(st, buf):
+    o, N = st._offsets, len(st)
+    f = buf[o["features"]: o["features"] + 48 * N].view(N, 16, 3)
+    return {"xyz": buf[o["xyz"]: o["xyz"] + 3 * N].view(N, 3), "scaling": buf[o["scaling"]: o["scaling"] + 3 * N].view(N, 3),
+            "rotation": buf[o["rotation"]: o["rotation"] + 4 * N].view(N, 4), "opacity": buf[o["opacity"]: o["opacity"] + N].view(N, 1),
+            "features_dc": f[:, 0:1], "features_rest": f[:, 1:]}
+
+
+@pytest.mark.parametrize("N,cap", [(20000, None), (20000, 20500), (20000, 20000), (3000, None), (1, None)])
+def test_densify_and_prune_matches_reference_bookkeeping(pkg, oracle, N, cap):
+    st, opt, ref = _setup(pkg, oracle, N, seed=31)
+    args = dict(thr=2e-4, min_opacity=0.05, extent=0.2)
+    torch.manual_seed(1234)
+    want = ref.densify_and_prune(args["thr"], args["min_opacity"], args["extent"], max_gaussians=cap)
+    torch.manual_seed(1234)
+    got = st.densify_and_prune(args["thr"], args["min_opacity"], args["extent"], None, optimizer=opt, max_gaussians=cap)
+    for k in ("cloned", "split", "pruned", "n_after"):
+        assert got[k] == want[k], (k, got, want)
+    assert len(st) == want["n_after"] and got["n_before"] == N
+    if N > 1000 and cap is None:
+        assert want["cloned"] > 0 and want["split"] > 0 and want["pruned"] > 0  # the case exercises all three
+    m, v = _moments(st, opt.exp_avg), _moments(st, opt.exp_avg_sq)
+    for a in ATTRS:
+        assert torch.equal(getattr(st, a).detach(), ref.p[a]), a
+        assert torch.equal(m[a], ref.m[a]) and torch.equal(v[a], ref.v[a]), a
+    assert st.xyz_gradient_accum.shape == (len(st), 3) and float(st.xyz_gradient_accum.abs().sum()) == 0.0
+    assert st.xyz_gradient_count.shape == (len(st), 1) and st.max_radii_2D.shape == (len(st),)
+    # the rebuilt store renders and trains
+    if len(st) > 0:
+        sc = oracle.synthetic_scene(4, 320, 200, seed=1)
+        res = st.render(sc["K"].to(DEV), {"world_view_transform": sc["viewmat"].to(DEV), "image_width": 320, "image_height": 200})
+        res["render"].sum().backward()
+        opt.step()
+        assert torch.isfinite(st.flat).all()
