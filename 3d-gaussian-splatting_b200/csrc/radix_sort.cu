@@ -120,55 +120,87 @@ struct __align__(16) RsSmem {
     uint32_t vals[RS_TILE];
     uint32_t warp_hist[RS_WARPS][RS_RADIX];  // per-warp digit counts -> exclusive offsets across warps
     uint32_t bin_excl[RS_RADIX];             // tile-local exclusive start of each digit
-    int64_t global_off[RS_RADIX];            // global index of smem slot p with digit d = global_off[d] + p
+    uint32_t global_off[RS_RADIX];           // global index of smem slot p with digit d = global_off[d] + p (mod 2^32)
     uint32_t warp_scan[RS_WARPS];
     uint32_t tile;
 };
 
-template <typename KeyT, bool USE_MATCH>
+// Lanes holding the same BITS-bit digit, four instructions per bit: predicate from the digit bit, ballot, and one
+// of two predicated LOP3 folding "lanes that disagree with me in this bit" into x (x |= bit ? ~vote : vote).
+template <int BITS>
+__device__ __forceinline__ unsigned digit_peers_n(uint32_t d) {
+    unsigned x = 0;
+#pragma unroll
+    for (int b = 0; b < BITS; ++b) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t.reg .b32 v, t;\n\t"
+            "and.b32 t, %1, %2;\n\t"
+            "setp.ne.u32 p, t, 0;\n\t"
+            "vote.sync.ballot.b32 v, p, 0xffffffff;\n\t"
+            "@p lop3.b32 %0, %0, v, 0, 0xF3;\n\t"
+            "@!p lop3.b32 %0, %0, v, 0, 0xFC;\n\t}"
+            : "+r"(x)
+            : "r"(d), "r"(1u << b));
+    }
+    return ~x;
+}
+
+// One LSD pass.  dmask selects the digit bits of this pass, BITS >= popcount(dmask) is the number of ballots spent.  All indices are 32-bit
+// (n < 2^30); full tiles take an unpredicated path.
+template <typename KeyT, int BITS>
 __global__ void __launch_bounds__(RS_THREADS)
 rs_onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                   KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n, int shift, int bits,
-                   const uint32_t* __restrict__ digit_base, volatile uint32_t* __restrict__ status,
+                   KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out, uint32_t n, int shift,
+                   uint32_t dmask, const uint32_t* __restrict__ digit_base, volatile uint32_t* __restrict__ status,
                    uint32_t* __restrict__ ticket) {
     extern __shared__ __align__(16) unsigned char rs_smem_raw[];
     RsSmem<KeyT>& S = *reinterpret_cast<RsSmem<KeyT>*>(rs_smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const uint32_t dmask = (1u << bits) - 1u;
 
     if (tid == 0) S.tile = atomicAdd(ticket, 1u);
     for (int i = tid; i < RS_WARPS * RS_RADIX; i += RS_THREADS) (&S.warp_hist[0][0])[i] = 0;
     __syncthreads();
     const uint32_t tile = S.tile;
-    const int64_t tile_base = (int64_t)tile * RS_TILE;
-    const int n_valid = (int)min((int64_t)RS_TILE, n - tile_base);
+    const uint32_t tile_base = tile * RS_TILE;
+    const uint32_t n_valid = min((uint32_t)RS_TILE, n - tile_base);
+    const bool full = n_valid == RS_TILE;
 
     // ---- load (warp-striped so that order inside a warp is item-major, lane-minor) ----
     KeyT key[RS_ITEMS];
     uint32_t val[RS_ITEMS];
     uint32_t pos[RS_ITEMS];
-    const int warp_base = wid * (32 * RS_ITEMS);
+    const uint32_t warp_base = wid * (32 * RS_ITEMS) + lane;
+    const KeyT* kin = keys_in + tile_base + warp_base;
+    const uint32_t* vin = vals_in + tile_base + warp_base;
+    if (full) {
 #pragma unroll
-    for (int i = 0; i < RS_ITEMS; ++i) {
-        int local = warp_base + i * 32 + lane;
-        bool ok = local < n_valid;
-        key[i] = ok ? keys_in[tile_base + local] : (KeyT)~(KeyT)0;
-        val[i] = ok ? vals_in[tile_base + local] : 0u;
+        for (int i = 0; i < RS_ITEMS; ++i) {
+            key[i] = kin[i * 32];
+            val[i] = vin[i * 32];
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < RS_ITEMS; ++i) {
+            const bool ok = warp_base + i * 32 < n_valid;
+            key[i] = ok ? kin[i * 32] : (KeyT)~(KeyT)0;
+            val[i] = ok ? vin[i * 32] : 0u;
+        }
     }
     // ---- rank inside the warp by digit, in order ----
     // The warp's histogram row is private to it, so the lowest lane of each digit group updates it
     // with a plain load + store (no shared atomics: ~2 cycles per distinct address, i.e. up to 60 cycles
     // per item for high-entropy digits); __syncwarp orders the row between successive items.
     const unsigned lt_mask = (1u << lane) - 1u;
+    uint32_t* my_row = S.warp_hist[wid];
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; ++i) {
-        uint32_t d = (uint32_t)((uint64_t)key[i] >> shift) & dmask;
-        unsigned peers = USE_MATCH ? __match_any_sync(0xffffffffu, d) : digit_peers(0xffffffffu, d);
-        int leader = __ffs(peers) - 1;
+        const uint32_t d = (uint32_t)(key[i] >> shift) & dmask;
+        const unsigned peers = digit_peers_n<BITS>(d);
+        const int leader = __ffs(peers) - 1;
         uint32_t base = 0;
         if (lane == leader) {
-            base = S.warp_hist[wid][d];
-            S.warp_hist[wid][d] = base + __popc(peers);
+            base = my_row[d];
+            my_row[d] = base + __popc(peers);
         }
         base = __shfl_sync(0xffffffffu, base, leader);
         pos[i] = base + __popc(peers & lt_mask);
@@ -210,7 +242,7 @@ rs_onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict_
     {
         uint32_t excl = 0;
         if (tile != 0) {
-            int64_t t = (int64_t)tile - 1;
+            int t = (int)tile - 1;
             bool found = false;
             while (!found) {
                 uint32_t s[RS_LOOKBACK];
@@ -227,28 +259,38 @@ rs_onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict_
             }
             *my = (excl + count) | FLAG_PREFIX;
         }
-        S.global_off[tid] = (int64_t)digit_base[tid] + (int64_t)excl - (int64_t)excl_local;
+        S.global_off[tid] = digit_base[tid] + excl - excl_local;  // wraps mod 2^32; global_off[d] + p is exact
     }
     __syncthreads();
     // ---- scatter into tile-local sorted order ----
 #pragma unroll
     for (int i = 0; i < RS_ITEMS; ++i) {
-        uint32_t d = (uint32_t)((uint64_t)key[i] >> shift) & dmask;
-        uint32_t p = S.bin_excl[d] + S.warp_hist[wid][d] + pos[i];
+        const uint32_t d = (uint32_t)(key[i] >> shift) & dmask;
+        const uint32_t p = S.bin_excl[d] + my_row[d] + pos[i];
         S.keys[p] = key[i];
         S.vals[p] = val[i];
     }
     __syncthreads();
     // ---- coalesced write-out ----
+    if (full) {
 #pragma unroll
-    for (int i = 0; i < RS_ITEMS; ++i) {
-        int p = i * RS_THREADS + tid;
-        if (p < n_valid) {
-            KeyT k = S.keys[p];
-            uint32_t d = (uint32_t)((uint64_t)k >> shift) & dmask;
-            int64_t o = S.global_off[d] + p;
+        for (int i = 0; i < RS_ITEMS; ++i) {
+            const uint32_t p = i * RS_THREADS + tid;
+            const KeyT k = S.keys[p];
+            const uint32_t o = S.global_off[(uint32_t)(k >> shift) & dmask] + p;
             keys_out[o] = k;
             vals_out[o] = S.vals[p];
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < RS_ITEMS; ++i) {
+            const uint32_t p = i * RS_THREADS + tid;
+            if (p < n_valid) {
+                const KeyT k = S.keys[p];
+                const uint32_t o = S.global_off[(uint32_t)(k >> shift) & dmask] + p;
+                keys_out[o] = k;
+                vals_out[o] = S.vals[p];
+            }
         }
     }
 }
@@ -281,8 +323,11 @@ int sort_pairs_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_t* vals
     cudaStream_t st = (cudaStream_t)stream;
     static bool attr_set = false;  // one flag per template instantiation
     if (!attr_set) {
-        cudaFuncSetAttribute(rs_onesweep_kernel<KeyT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem<KeyT>) + 160 * 1024);
-        cudaFuncSetAttribute(rs_onesweep_kernel<KeyT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RsSmem<KeyT>) + 160 * 1024);
+        const int smem_max = (int)sizeof(RsSmem<KeyT>) + 160 * 1024;
+        cudaFuncSetAttribute(rs_onesweep_kernel<KeyT, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
+        cudaFuncSetAttribute(rs_onesweep_kernel<KeyT, 7>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
+        cudaFuncSetAttribute(rs_onesweep_kernel<KeyT, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
+        cudaFuncSetAttribute(rs_onesweep_kernel<KeyT, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
         attr_set = true;
     }
     const size_t ntiles = (size_t)((M + RS_TILE - 1) / RS_TILE);
@@ -297,8 +342,6 @@ int sort_pairs_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_t* vals
     }
     static int pad = -1;
     if (pad < 0) { const char* e = getenv("B200_SORT_SMEM_PAD"); pad = e ? atoi(e) : 0; }
-    static int use_match = -1;
-    if (use_match < 0) { const char* e = getenv("B200_SORT_MATCH"); use_match = (e && e[0] == '1') ? 1 : 0; }
     static int hb = -1;
     if (hb < 0) { const char* e = getenv("B200_HIST_BLOCKS"); hb = e ? atoi(e) : 148 * 2; }
     int hist_blocks = (int)min((int64_t)hb, (M + 255) / 256);
@@ -309,15 +352,15 @@ int sort_pairs_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_t* vals
     }
     const uint32_t* bases = prepared_base ? prepared_base : hist;
     KeyT* kin = keys_a; uint32_t* vin = vals_a; KeyT* kout = keys_b; uint32_t* vout = vals_b;
+    const size_t smem = sizeof(RsSmem<KeyT>) + pad;
     for (int p = 0; p < npasses; ++p) {
         int shift = p * RS_BITS;
         int bits = (end_bit - shift) < RS_BITS ? (end_bit - shift) : RS_BITS;
-        if (use_match)
-            rs_onesweep_kernel<KeyT, true><<<(unsigned)ntiles, RS_THREADS, sizeof(RsSmem<KeyT>) + pad, st>>>(
-                kin, vin, kout, vout, M, shift, bits, bases + p * RS_RADIX, status + (size_t)p * ntiles * RS_RADIX, tickets + p);
-        else
-            rs_onesweep_kernel<KeyT, false><<<(unsigned)ntiles, RS_THREADS, sizeof(RsSmem<KeyT>) + pad, st>>>(
-                kin, vin, kout, vout, M, shift, bits, bases + p * RS_RADIX, status + (size_t)p * ntiles * RS_RADIX, tickets + p);
+#define RS_LAUNCH(B) rs_onesweep_kernel<KeyT, B><<<(unsigned)ntiles, RS_THREADS, smem, st>>>( \
+        kin, vin, kout, vout, (uint32_t)M, shift, (1u << bits) - 1u, bases + p * RS_RADIX, status + (size_t)p * ntiles * RS_RADIX, tickets + p)
+        // digits narrower than 5 bits run the 5-bit kernel (the upper ballots see zeros): same result
+        if (bits >= 8) RS_LAUNCH(8); else if (bits == 7) RS_LAUNCH(7); else if (bits == 6) RS_LAUNCH(6); else RS_LAUNCH(5);
+#undef RS_LAUNCH
         KeyT* tk = kin; kin = kout; kout = tk;
         uint32_t* tv = vin; vin = vout; vout = tv;
     }
