@@ -10,6 +10,9 @@
 
 namespace {
 
+#ifndef RB_MIN_WARPS
+#define RB_MIN_WARPS 24          // resident warps per SM the register allocation must allow (<= 85 registers)
+#endif
 #define RB_GROUP 4            // Gaussians whose per-lane partial sums wait in shared memory for one reduction
 #define RB_ROW (32 * 3)       // float4 per waiting Gaussian: 32 lanes x {q0, q1, q2}
 
@@ -55,7 +58,7 @@ __device__ __forceinline__ void flush_pending(const float4* __restrict__ part, c
 }
 
 template <int CHSET, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32)
+__global__ void __launch_bounds__(WARPS * 32, RB_MIN_WARPS / WARPS)
 raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__ flatten_ids,
                   const int32_t* __restrict__ offsets, int M, int W, int H, int tile_w, int n_tiles,
                   const float* __restrict__ background, int n_bg, const float* __restrict__ alpha_in,

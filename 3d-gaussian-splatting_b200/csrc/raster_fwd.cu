@@ -3,10 +3,14 @@
 #include <stdlib.h>
 #include "raster_common.cuh"
 
+#ifndef RF_MIN_WARPS
+#define RF_MIN_WARPS 32  // resident warps per SM the register allocation must allow
+#endif
+
 namespace {
 
 template <int CHSET, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32)
+__global__ void __launch_bounds__(WARPS * 32, RF_MIN_WARPS / WARPS)
 raster_fwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__ flatten_ids,
                   const int32_t* __restrict__ offsets, int M, int W, int H, int tile_w, int n_tiles,
                   const float* __restrict__ background, int n_bg, float* __restrict__ render, float* __restrict__ alpha_out, int32_t* __restrict__ last_ids) {
