@@ -153,6 +153,7 @@ bin_emit_sorted_kernel(const float* __restrict__ splats, const int32_t* __restri
                        uint16_t* __restrict__ tile_keys, int32_t* __restrict__ flatten_ids) {
     __shared__ int s_excl[EMIT_THREADS + 1];
     __shared__ int s_minx[EMIT_THREADS], s_miny[EMIT_THREADS], s_bw[EMIT_THREADS], s_g[EMIT_THREADS];
+    __shared__ float s_rbw[EMIT_THREADS];
     __shared__ int s_warp[EMIT_THREADS / 32];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int64_t i = (int64_t)blockIdx.x * EMIT_THREADS + tid;
@@ -170,6 +171,7 @@ bin_emit_sorted_kernel(const float* __restrict__ splats, const int32_t* __restri
             int maxx = (int)fminf(fmaxf(ceilf(tile_x + trx), 0.f), fw);
             int miny = (int)fminf(fmaxf(floorf(tile_y - try_), 0.f), fh);
             s_minx[tid] = minx; s_miny[tid] = miny; s_bw[tid] = maxx - minx; s_g[tid] = g;
+            s_rbw[tid] = 1.f / (float)(maxx - minx);
         }
     }
     int inc = cnt;
@@ -197,7 +199,9 @@ bin_emit_sorted_kernel(const float* __restrict__ splats, const int32_t* __restri
         }
         const int kk = k - s_excl[lo];
         const int bw = s_bw[lo];
-        const int ty = s_miny[lo] + kk / bw, tx = s_minx[lo] + kk % bw;
+        // row = kk / bw without an integer division: kk < 65536 tiles, so (kk + 0.5) / bw in fp32 floors exactly
+        const int row = (int)(((float)kk + 0.5f) * s_rbw[lo]);
+        const int ty = s_miny[lo] + row, tx = s_minx[lo] + (kk - row * bw);
         const int64_t out = boff + k;
         if (out < M) {
             tile_keys[out] = (uint16_t)(ty * tile_w + tx);
