@@ -21,42 +21,45 @@ def shard_views(n_views: int, rank: int, world_size: int) -> List[int]:
     return list(range(rank, n_views, world_size))
 
 
-def _flat_numel(params: Sequence[torch.Tensor]) -> int:
-    return sum(p.numel() for p in params)
-
-
 def allreduce_gradients(params: Iterable[torch.Tensor], n_global_views: int, group=None,
                         flat: torch.Tensor = None) -> torch.Tensor:
-    """Sum-all-reduce every ``p.grad`` through one contiguous fp32 buffer (59*N floats for the six
-    Gaussian attributes), then scale by 1/n_global_views so the result is the gradient of the MEAN
+    """Sum-all-reduce every ``p.grad`` and scale by 1/n_global_views, so the result is the gradient of the MEAN
     per-view loss.  Local gradients must be those of the SUM of the rank's per-view losses.
-    Returns the flat buffer (reusable via ``flat=``)."""
+
+    When the gradients are views of ONE flat buffer (``GaussianStore.flat_grad``, or ``flat=`` from a previous call
+    whose views are still attached) that buffer is reduced by a single collective with no copies.  Otherwise the
+    per-attribute gradient tensors are reduced in place by collectives issued back to back (one NCCL group on the
+    wire) and scaled by one fused multiply: no flatten / unflatten passes over the 59*N floats.
+    Returns the flat buffer if one was used, else None."""
     params = [p for p in params if p.requires_grad]
-    n = _flat_numel(params)
-    dev = params[0].device
-    if flat is None or flat.numel() != n or flat.device != dev:
-        flat = torch.empty(n, dtype=torch.float32, device=dev)
-    off = 0
     for p in params:
-        k = p.numel()
         if p.grad is None:
-            flat[off:off + k].zero_()
-        else:
-            flat[off:off + k].copy_(p.grad.reshape(-1))
-        off += k
-    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
-        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
-    flat.mul_(1.0 / float(n_global_views))
-    off = 0
-    for p in params:
-        k = p.numel()
-        g = flat[off:off + k].view_as(p)
-        if p.grad is None:
-            p.grad = g.clone()
-        else:
-            p.grad.copy_(g)
-        off += k
-    return flat
+            p.grad = torch.zeros_like(p)
+    grads = [p.grad for p in params]
+    multi = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+    scale = 1.0 / float(n_global_views)
+    if flat is not None and _views_of(flat, grads):
+        if multi:
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+        flat.mul_(scale)
+        return flat
+    if multi:
+        works = [dist.all_reduce(g, op=dist.ReduceOp.SUM, group=group, async_op=True) for g in grads]
+        for w in works:
+            w.wait()
+    torch._foreach_mul_(grads, scale)
+    return None
+
+
+def _views_of(flat: torch.Tensor, grads: Sequence[torch.Tensor]) -> bool:
+    """True if every gradient is a contiguous slice of ``flat`` and together they cover it in order."""
+    base, end = flat.data_ptr(), flat.data_ptr() + flat.numel() * flat.element_size()
+    total = 0
+    for g in grads:
+        if not g.is_contiguous() or g.dtype != flat.dtype or not (base <= g.data_ptr() < end):
+            return False
+        total += g.numel()
+    return total <= flat.numel()
 
 
 class ViewShardedStep:

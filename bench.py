@@ -32,6 +32,7 @@ CONFIGS = {
     "tiny": (20_000, 320, 192, 3),
 }
 METRIC = "fwd+bwd Mpix/s (1M gaussians SH3, 1920x1080)"
+LAST_PAIRS = None  # (pixel x Gaussian pairs visited, composited) by the CPU port's last forward blend
 
 
 def _peaks():
@@ -136,6 +137,8 @@ def cpu_port_time(N, W, H, deg, steps, warmup, seed=0):
         M = out["M"]
         if i >= warmup:
             times.append(dt)
+    global LAST_PAIRS
+    LAST_PAIRS = cpu_port.pairs_evaluated()
     return sum(times) / len(times), cpu_port.num_threads(), M
 
 
@@ -424,7 +427,9 @@ def run_b200(args):
         # bounded sample of the same workload on the host cores: one full view, C/OpenMP port of the oracle
         sec, cores, Mc = cpu_port_time(N, W, H, deg, steps=1, warmup=0)
         cpu_baseline = {"value": W * H / sec / 1e6, "unit": "Mpix/s", "cores": cores, "kind": "port",
-                        "sample": f"1 full view fwd+bwd (N={N}, {W}x{H}, M={Mc}), oracle/cpu_splat.c OpenMP"}
+                        "sample": f"1 full view fwd+bwd (N={N}, {W}x{H}, M={Mc}), oracle/cpu_splat.c OpenMP",
+                        "P_pairs_visited": LAST_PAIRS[0] if LAST_PAIRS else None,
+                        "P_pairs_composited": LAST_PAIRS[1] if LAST_PAIRS else None}
     except LookupError as e:
         cpu_baseline = {"value": None, "unit": "Mpix/s", "cores": 0, "kind": "port", "sample": str(e)}
     except Exception as e:
@@ -435,7 +440,7 @@ def run_b200(args):
         "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.config}: {N} gaussians SH{deg}, {W}x{H}, {V} view(s)/rank/step fwd+bwd"
-                               + (", 1 NCCL all-reduce of 59N-float flat gradient/step" if world > 1 else ""),
+                               + (", gradients all-reduced in place (5 attribute tensors back to back; the store path reduces ONE flat 59N-float buffer) once per step" if world > 1 else ""),
                    "N": N, "N_visible": n_vis, "M_isects": M, "views_per_rank": V,
                    "l2": "inputs larger than L2 (params 236 MB + keys/records > 126 MB); no explicit flush"},
         "e2e": {"value": e2e_val, "unit": "Mpix/s", "h2d_bytes_per_step": V * (W * H * 3 * 4 + 64), "d2h_bytes_per_step": 4,

@@ -25,6 +25,8 @@ def _load():
     lib = C.CDLL(_SO)
     lib.cpu_num_threads.restype = C.c_int
     lib.cpu_cumsum.restype = C.c_int64
+    lib.cpu_pairs_evaluated.restype = C.c_longlong
+    lib.cpu_pairs_blended.restype = C.c_longlong
     return lib
 
 
@@ -34,6 +36,11 @@ _p = lambda t: C.c_void_p(t.data_ptr()) if t is not None else None  # noqa: E731
 
 def num_threads() -> int:
     return int(_lib.cpu_num_threads())
+
+
+def pairs_evaluated():
+    """(pairs visited, pairs composited) of the last forward blend — P of SURVEY.md §8(d)."""
+    return int(_lib.cpu_pairs_evaluated()), int(_lib.cpu_pairs_blended())
 
 
 def set_threads(n: int) -> None:

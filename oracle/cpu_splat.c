@@ -278,11 +278,18 @@ void cpu_tile_ranges(const int64_t* ids, int64_t M, int n_tiles, int32_t* offset
  * A.4 forward blend (gsplat rasterize_to_pixels fwd); CH = 3 (rgb), 1 (depth) or 4 (rgb+depth):
  * feat[N,CH] is the per-Gaussian feature vector composited.
  * ------------------------------------------------------------------------------------------- */
+/* P of SURVEY.md §8(d): (pixel, Gaussian) pairs evaluated by the last cpu_raster_fwd call (pairs visited before a
+ * pixel terminates), and how many of them were composited. */
+static long long g_pairs_evaluated = 0, g_pairs_blended = 0;
+long long cpu_pairs_evaluated(void) { return g_pairs_evaluated; }
+long long cpu_pairs_blended(void) { return g_pairs_blended; }
+
 void cpu_raster_fwd(const float* means2d, const float* conics, const float* feat, int CH, const float* opac,
                     const int32_t* flatten_ids, const int32_t* offsets, int64_t M, int W, int H, const float* bg,
                     float* render, float* alpha, int32_t* last_ids) {
     int tile_w = (W + TILE - 1) / TILE, tile_h = (H + TILE - 1) / TILE, n_tiles = tile_w * tile_h;
-#pragma omp parallel for schedule(dynamic, 4)
+    long long pairs = 0, blended = 0;
+#pragma omp parallel for schedule(dynamic, 4) reduction(+ : pairs, blended)
     for (int t = 0; t < n_tiles; ++t) {
         int start = offsets[t], end = (t + 1 < n_tiles) ? offsets[t + 1] : (int)M;
         int ty = t / tile_w, tx = t % tile_w;
@@ -293,6 +300,7 @@ void cpu_raster_fwd(const float* means2d, const float* conics, const float* feat
                 float px = ix + 0.5f, py = iy + 0.5f, T = 1.f, acc[4] = {0, 0, 0, 0};
                 int last = -1;
                 for (int idx = start; idx < end; ++idx) {
+                    ++pairs;
                     int g = flatten_ids[idx];
                     float dx = means2d[2 * g] - px, dy = means2d[2 * g + 1] - py;
                     float sigma = 0.5f * (conics[3 * g] * dx * dx + conics[3 * g + 2] * dy * dy) + conics[3 * g + 1] * dx * dy;
@@ -303,6 +311,7 @@ void cpu_raster_fwd(const float* means2d, const float* conics, const float* feat
                     float w = al * T;
                     for (int c = 0; c < CH; ++c) acc[c] += w * feat[(size_t)g * CH + c];
                     last = idx; T = Tn;
+                    ++blended;
                 }
                 size_t pix = (size_t)iy * W + ix;
                 for (int c = 0; c < CH; ++c) render[pix * CH + c] = acc[c] + T * (bg ? bg[c] : 0.f);
@@ -310,6 +319,8 @@ void cpu_raster_fwd(const float* means2d, const float* conics, const float* feat
                 last_ids[pix] = last;
             }
     }
+    g_pairs_evaluated = pairs;
+    g_pairs_blended = blended;
 }
 
 /* ---------------------------------------------------------------------------------------------
