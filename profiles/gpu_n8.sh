@@ -1,0 +1,3 @@
+N=${1:-8}
+python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29521 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo rc=$?
+tail -3 gpurun_out/bench_n$N.err | cut -c1-300; python profiles/show_bench.py gpurun_out/bench_n$N.json
