@@ -244,7 +244,7 @@ def run_b200(args):
 
     def step_e2e(step):
         """through the public backend call with HOST buffers: pose + ground-truth frame uploaded from pinned
-        memory every view, L1 loss, backward, loss read back (what trainer.py:270-281,485-497 does per view)."""
+        memory every view, L1 + D-SSIM loss, backward, loss read back (what trainer.py:270-281,485-497 does per view)."""
         nonlocal flat
         cur = torch.cuda.current_stream()
         for p in params_list:
@@ -263,7 +263,8 @@ def run_b200(args):
             cur.wait_event(ready_ev[slot])
             vp = {"world_view_transform": pose_slot[slot], "image_width": W, "image_height": H}
             res = backend.render_with_depth(leaves, vp, bg_color=bg, render_mode="RGB", device="cuda", sh_degree=deg)
-            loss = (res["render"] - gt_slot[slot]).abs().mean()
+            # the reference's per-view loss (trainer.py:485-492: clamp, L1 + 0.2 D-SSIM), value and gradient in one kernel
+            loss = pkg.l1_ssim_loss(res["render"], gt_slot[slot], 0.2)["loss"]
             loss.backward()
             free_ev[slot].record(cur)
             tot = tot + loss.detach()
