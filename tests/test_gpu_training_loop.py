@@ -1,0 +1,177 @@
+"""BASELINE.json configs[0] substitute: the reference's own training step driven for a few hundred
+iterations on a small synthetic scene, once with the CPU oracle behind the backend interface and once with the
+B200 backend — the loss curves must track each other.
+
+The reference's configs[0] (`src/train.py` on `data/input.mp4` "via the existing torch rasterizer backend on
+CPU") cannot run as stated: `src/backends/pytorch_backend.py:2-5` raises NotImplementedError and the video
+pipeline needs LoFTR weights that are not in the image.  What is exercised here instead is everything between the
+view tensors and the optimiser, restated from the reference:
+
+  * `_training_step`       src/training/trainer.py:445-520 (zero_grad, per-view render -> _stclamp -> L1 + SSIM,
+                           mean over the batch, + scale-ratio regulariser, backward, Adam step)
+  * `_stclamp`             trainer.py:102-107,  `_compute_ssim` trainer.py:354-371,  `_scale_ratio_reg` :436-443
+  * optimiser groups       trainer.py:331-340 (Adam, lr 0, eps 1e-15, per-group learning rates)
+  * getters                src/gaussians/gaussian_model.py:90-108
+
+The oracle arm is test infrastructure (oracle/cpu_splat.c through oracle/cpu_port.py wrapped in an autograd
+Function); the product arm is `B200Backend.render_with_depth`, and a third arm runs the fused f1/f3/f4 path
+(GaussianStore.render + l1_ssim_loss + StoreAdam) on the same problem.
+"""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+W, H, N, DEG = 160, 90, 20000, 3
+ITERS, BATCH, LAMBDA = 300, 2, 0.2
+LRS = {"xyz": 1.6e-4, "features_dc": 0.0025, "features_rest": 0.0025 / 20.0, "opacity": 0.05, "scaling": 0.005,
+       "rotation": 0.001}
+KEYS = ("xyz", "features_dc", "features_rest", "opacity", "scaling", "rotation")
+
+
+class _OracleRender(torch.autograd.Function):
+    """CPU oracle behind autograd: forward = cpu_port.forward, backward = cpu_port.backward."""
+
+    @staticmethod
+    def forward(ctx, means, scales, quats, opac, shs, viewmat, K):
+        from oracle import cpu_port
+        act = {"means3D": means, "scales": scales, "rotations": quats, "opacities": opac, "shs": shs}
+        fw = cpu_port.forward(act, viewmat, K, W, H, DEG, bg=torch.zeros(3))
+        ctx.fw = fw
+        return fw["render"]
+
+    @staticmethod
+    def backward(ctx, v_render):
+        from oracle import cpu_port
+        g = cpu_port.backward(ctx.fw, W, H, DEG, v_render.contiguous())
+        return g["means3D"], g["scales"], g["rotations"], g["opacities"].reshape(-1, 1), g["shs"], None, None
+
+
+class _OracleBackend:
+    """Same interface as the reference's GSplatBackend.render_with_depth (gsplat_backend.py:118-205), CPU oracle inside."""
+
+    def __init__(self, K):
+        self.K = K
+
+    def render_with_depth(self, gaussians, viewpoint, bg_color=None, render_mode="RGB", device="cpu", sh_degree=3):
+        img = _OracleRender.apply(gaussians["means3D"], gaussians["scales"], gaussians["rotations"],
+                                  gaussians["opacities"], gaussians["shs"], viewpoint["world_view_transform"], self.K)
+        return {"render": img}
+
+
+def _getters(raw):
+    return {"means3D": raw["xyz"], "scales": torch.exp(raw["scaling"]),
+            "rotations": F.normalize(raw["rotation"], dim=-1), "opacities": torch.sigmoid(raw["opacity"]),
+            "shs": torch.cat([raw["features_dc"], raw["features_rest"]], dim=1)}
+
+
+def _stclamp(x):
+    return x + (x.clamp(0.0, 1.0) - x).detach()
+
+
+def _ssim(a, b):
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    pool = lambda t: F.avg_pool2d(t, 3, 1, padding=1)
+    mu1, mu2 = pool(a), pool(b)
+    s1, s2, s12 = pool(a * a) - mu1 * mu1, pool(b * b) - mu2 * mu2, pool(a * b) - mu1 * mu2
+    return (((2 * mu1 * mu2 + C1) * (2 * s12 + C2)) / ((mu1 * mu1 + mu2 * mu2 + C1) * (s1 + s2 + C2))).mean()
+
+
+def _scale_reg(scales):
+    ratio = scales.amax(dim=-1) / scales.amin(dim=-1).clamp(min=1e-8)
+    return 0.1 * (ratio.clamp(min=10.0) - 10.0).mean()
+
+
+def _training_step(raw, backend, batch, optimizer, device):
+    optimizer.zero_grad()
+    params = _getters(raw)
+    total = torch.tensor(0.0, device=device)
+    for view in batch:
+        viewpoint = {"world_view_transform": view["pose"], "image_width": W, "image_height": H}
+        img = backend.render_with_depth(params, viewpoint, bg_color=torch.zeros(3, device=device), render_mode="RGB",
+                                        device=device, sh_degree=DEG)["render"]
+        x = _stclamp(img)
+        l1 = F.l1_loss(x, view["image"])
+        ssim = _ssim(x.permute(2, 0, 1).unsqueeze(0).contiguous(), view["image"].permute(2, 0, 1).unsqueeze(0).contiguous())
+        total = total + (1.0 - LAMBDA) * l1 + LAMBDA * (1.0 - ssim)
+    total = total / len(batch) + _scale_reg(params["scales"])
+    total.backward()
+    optimizer.step()
+    return float(total.item())
+
+
+def _problem(oracle):
+    """Ground truth = the seeded scene rendered by the oracle from four cameras; the model starts perturbed."""
+    from oracle import cpu_port
+    truth = oracle.synthetic_scene(N, W, H, seed=21)
+    cams = oracle.circle_cameras(8, radius=0.5)[[0, 1, 2, 7]]
+    K = truth["K"]
+    act = oracle.activate(truth)
+    views = [{"pose": vm, "image": cpu_port.forward(act, vm, K, W, H, DEG, bg=torch.zeros(3))["render"].clamp(0, 1)}
+             for vm in cams]
+    g = torch.Generator().manual_seed(5)
+    start = {k: truth[k].clone() for k in KEYS}
+    start["xyz"] += 0.01 * torch.randn(N, 3, generator=g)
+    start["features_dc"] += 0.3 * torch.randn(N, 1, 3, generator=g)
+    start["scaling"] += 0.2 * torch.randn(N, 3, generator=g)
+    start["opacity"] += 0.5 * torch.randn(N, 1, generator=g)
+    return start, views, K
+
+
+def _schedule():
+    g = torch.Generator().manual_seed(9)
+    return [torch.randperm(4, generator=g)[:BATCH].tolist() for _ in range(ITERS)]
+
+
+def _run(start, views, K, backend_ctor, device):
+    raw = {k: v.to(device).clone().requires_grad_(True) for k, v in start.items()}
+    opt = torch.optim.Adam([{"params": [raw[k]], "lr": LRS[k], "name": k} for k in KEYS], lr=0.0, eps=1e-15)
+    backend = backend_ctor(K.to(device))
+    vs = [{"pose": v["pose"].to(device), "image": v["image"].to(device)} for v in views]
+    return [_training_step(raw, backend, [vs[i] for i in idx], opt, device) for idx in _schedule()]
+
+
+@pytest.fixture(scope="module")
+def curves(pkg, oracle):
+    start, views, K = _problem(oracle)
+    cpu = _run(start, views, K, _OracleBackend, "cpu")
+    gpu = _run(start, views, K, pkg.B200Backend, "cuda")
+    return start, views, K, cpu, gpu
+
+
+def test_loss_curve_tracks_the_oracle_backend(curves):
+    _, _, _, cpu, gpu = curves
+    assert cpu[-1] < 0.8 * cpu[0], "the problem must actually train"
+    rel = max(abs(a - b) / a for a, b in zip(cpu, gpu))
+    print(f"loss {cpu[0]:.5f} -> {cpu[-1]:.5f} (oracle) / {gpu[-1]:.5f} (B200); max relative gap {rel:.2e}")
+    assert rel <= 0.01, rel                      # curves track within 1 %
+    assert abs(cpu[0] - gpu[0]) / cpu[0] <= 1e-5  # and the first step, before any divergence can compound, is tight
+
+
+def test_fused_store_loss_adam_path_tracks_too(pkg, curves):
+    start, views, K, cpu, _ = curves
+    dev = "cuda"
+    st = pkg.GaussianStore.from_tensors(start["xyz"].to(dev), start["features_dc"].to(dev),
+                                        start["features_rest"].to(dev), start["scaling"].to(dev),
+                                        start["rotation"].to(dev), start["opacity"].to(dev))
+    opt = pkg.StoreAdam(st, LRS, eps=1e-15)
+    Kd = K.to(dev)
+    vs = [{"pose": v["pose"].to(dev), "image": v["image"].to(dev).contiguous()} for v in views]
+    losses = []
+    for idx in _schedule():
+        st.zero_grad()
+        total = torch.zeros((), device=dev)
+        for i in idx:
+            res = st.render(Kd, {"world_view_transform": vs[i]["pose"], "image_width": W, "image_height": H},
+                            bg_color=torch.zeros(3, device=dev), sh_degree=DEG)
+            loss = pkg.l1_ssim_loss(res["render"], vs[i]["image"], LAMBDA)["loss"] / len(idx)
+            loss.backward()
+            total = total + loss.detach()
+        reg = _scale_reg(st.get_scaling)
+        reg.backward()
+        opt.step()
+        losses.append(float((total + reg.detach()).item()))
+    rel = max(abs(a - b) / a for a, b in zip(cpu, losses))
+    print(f"fused path: final loss {losses[-1]:.5f}; max relative gap to the oracle arm {rel:.2e}")
+    assert rel <= 0.01, rel
