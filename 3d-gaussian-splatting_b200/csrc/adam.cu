@@ -8,6 +8,9 @@
 // rest, which is how the reference's separate features_dc / features_rest groups map onto the [N,16,3] layout.
 // Arithmetic follows torch.optim.Adam (no amsgrad, no weight decay, not maximize):
 //   m = b1 m + (1-b1) g;  v = b2 v + (1-b2) g^2;  p -= (lr / (1-b1^t)) * m / (sqrt(v) / sqrt(1-b2^t) + eps)
+// A segment may carry an upper bound applied to the updated parameter in the same pass — the reference's
+// per-iteration hard cap on the log-scales, `gaussians.scaling.data.clamp_(max=scale_ceiling)`
+// (trainer.py:854-859), which otherwise is one more read+write of the scaling block per step.
 #include "common.cuh"
 
 #define ADAM_MAX_SEG 8
@@ -16,6 +19,7 @@ struct AdamSeg {
     long long begin, end;   // element range in the flat buffer (multiples of 4)
     float lr, lr_alt;       // lr_alt applies where (i - begin) % period >= split
     int period, split;      // period == 0: one rate for the whole segment
+    float clamp_max;        // updated parameters are min(p, clamp_max); +inf = no bound
 };
 struct AdamSegs { AdamSeg s[ADAM_MAX_SEG]; int n; };
 
@@ -53,7 +57,7 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
         ma[j] = b1 * ma[j] + (1.f - b1) * gj;           // torch: exp_avg.lerp_(grad, 1 - beta1)
         va[j] = b2 * va[j] + (1.f - b2) * gj * gj;      // exp_avg_sq.mul_(b2).addcmul_(grad, grad, 1 - b2)
         const float denom = sqrtf(va[j]) * inv_sqrt_bc2 + eps;
-        pa[j] -= (lr * inv_bc1) * (ma[j] / denom);
+        pa[j] = fminf(pa[j] - (lr * inv_bc1) * (ma[j] / denom), sg.clamp_max);
     }
     reinterpret_cast<float4*>(p)[i4] = pp;
     reinterpret_cast<float4*>(m)[i4] = mm;
@@ -62,7 +66,8 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
 
 }  // namespace
 
-// seg_host: n_seg rows of 6 doubles {begin, end, lr, lr_alt, period, split}; step >= 1 is Adam's t.
+// seg_host: n_seg rows of B200_ADAM_SEG_DOUBLES (7) doubles {begin, end, lr, lr_alt, period, split, clamp_max};
+// clamp_max = +inf for "no bound"; step >= 1 is Adam's t.
 extern "C" int b200_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n_floats,
                               const double* seg_host, int n_seg, int step, float beta1, float beta2, float eps,
                               void* stream) {
@@ -73,10 +78,11 @@ extern "C" int b200_adam_step(float* params, const float* grads, float* exp_avg,
     AdamSegs segs;
     segs.n = n_seg;
     for (int k = 0; k < n_seg; ++k) {
-        const double* r = seg_host + 6 * k;
+        const double* r = seg_host + 7 * k;
         segs.s[k].begin = (long long)r[0]; segs.s[k].end = (long long)r[1];
         segs.s[k].lr = (float)r[2]; segs.s[k].lr_alt = (float)r[3];
         segs.s[k].period = (int)r[4]; segs.s[k].split = (int)r[5];
+        segs.s[k].clamp_max = (float)r[6];
         B200_REQUIRE(segs.s[k].begin % 4 == 0 && segs.s[k].begin >= 0 && segs.s[k].end <= n_floats, "bad segment");
     }
     const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);

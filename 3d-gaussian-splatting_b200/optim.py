@@ -4,11 +4,15 @@ src/training/trainer.py:331-340) as one kernel over the flat GaussianStore buffe
 ``lrs`` uses the reference's group names (``xyz, f_dc, f_rest, opacity, scaling, rotation``; the store's attribute
 names ``features_dc`` / ``features_rest`` are accepted too) and stays mutable, so the trainer's per-iteration
 position-rate schedule (``_update_learning_rate``, trainer.py:373-383) is ``opt.lrs["xyz"] = lr``.
+
+``scale_ceiling`` (mutable attribute, log-space, None = off) folds the reference's per-iteration hard cap on the
+scales, ``gaussians.scaling.data.clamp_(max=math.log(scene_extent * scale_clamp_ratio + 1e-9))``
+(trainer.py:854-859), into the same kernel: the updated log-scale is ``min(p, scale_ceiling)``.
 """
 from __future__ import annotations
 
 import ctypes as C
-from typing import Dict, Tuple
+from typing import Dict, Optional, Tuple
 
 import torch
 
@@ -18,8 +22,10 @@ _ALIASES = {"features_dc": "f_dc", "features_rest": "f_rest"}
 
 
 class StoreAdam:
-    def __init__(self, store, lrs: Dict[str, float], betas: Tuple[float, float] = (0.9, 0.999), eps: float = 1e-15):
+    def __init__(self, store, lrs: Dict[str, float], betas: Tuple[float, float] = (0.9, 0.999), eps: float = 1e-15,
+                 scale_ceiling: Optional[float] = None):
         self.store = store
+        self.scale_ceiling = scale_ceiling
         self.lrs = {_ALIASES.get(k, k): float(v) for k, v in lrs.items()}
         missing = {"xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation"} - set(self.lrs)
         if missing:
@@ -32,12 +38,14 @@ class StoreAdam:
     def _segments(self):
         st, n = self.store, len(self.store)
         o = st._offsets
+        inf = float("inf")
+        cap = inf if self.scale_ceiling is None else float(self.scale_ceiling)
         rows = [
-            (o["xyz"], o["xyz"] + 3 * n, self.lrs["xyz"], 0.0, 0, 0),
-            (o["scaling"], o["scaling"] + 3 * n, self.lrs["scaling"], 0.0, 0, 0),
-            (o["rotation"], o["rotation"] + 4 * n, self.lrs["rotation"], 0.0, 0, 0),
-            (o["opacity"], o["opacity"] + n, self.lrs["opacity"], 0.0, 0, 0),
-            (o["features"], o["features"] + 48 * n, self.lrs["f_dc"], self.lrs["f_rest"], 48, 3),
+            (o["xyz"], o["xyz"] + 3 * n, self.lrs["xyz"], 0.0, 0, 0, inf),
+            (o["scaling"], o["scaling"] + 3 * n, self.lrs["scaling"], 0.0, 0, 0, cap),
+            (o["rotation"], o["rotation"] + 4 * n, self.lrs["rotation"], 0.0, 0, 0, inf),
+            (o["opacity"], o["opacity"] + n, self.lrs["opacity"], 0.0, 0, 0, inf),
+            (o["features"], o["features"] + 48 * n, self.lrs["f_dc"], self.lrs["f_rest"], 48, 3, inf),
         ]
         flat = [float(x) for r in rows for x in r]
         return (C.c_double * len(flat))(*flat), len(rows)

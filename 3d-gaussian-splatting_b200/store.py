@@ -306,3 +306,88 @@ class GaussianStore(nn.Module):
             self.scaling.data[pos] = child_scaling[child]
         stats["n_after"] = self._n
         return stats
+
+    # ------------------------------------------------------------------ periodic opacity reset
+    @torch.no_grad()
+    def reset_opacity(self, ceiling: float = 0.01) -> None:
+        """trainer.py:841-850: every ``opacity_reset_interval`` iterations every opacity is pulled down to at most
+        ``ceiling`` (``logit(clamp(min(sigmoid(o), ceiling), 1e-6, 1 - 1e-6))``), in place on the flat buffer; the
+        optimiser moments are left alone, as in the reference."""
+        target = torch.minimum(self.get_opacity, torch.full_like(self.opacity, ceiling)).clamp(min=1e-6, max=1.0 - 1e-6)
+        self.opacity.copy_(torch.logit(target))
+
+    # ------------------------------------------------------------------ checkpoint / PLY wire format (§8 "later" row)
+    _REF_KEYS = ("xyz", "features_dc", "features_rest", "scaling", "rotation", "opacity")
+
+    def reference_state_dict(self) -> Dict[str, torch.Tensor]:
+        """The reference's ``GaussianModel.state_dict()`` (``model_state`` of trainer.py:384-395): six tensors under the
+        reference's names and shapes, detached copies."""
+        return {k: getattr(self, k).detach().clone() for k in self._REF_KEYS}
+
+    @classmethod
+    def from_reference_state_dict(cls, sd: Dict[str, torch.Tensor], device: str = "cuda") -> "GaussianStore":
+        """Build a store from a reference checkpoint's ``model_state`` (or a dict wrapping it, export.py:15-23)."""
+        for k in ("model_state", "state_dict"):
+            if k in sd and isinstance(sd[k], dict):
+                sd = sd[k]
+        missing = [k for k in cls._REF_KEYS if k not in sd]
+        if missing:
+            raise KeyError(f"reference state dict lacks {missing}")
+        return cls.from_tensors(*(sd[k].to(device=device, dtype=torch.float32) for k in
+                                  ("xyz", "features_dc", "features_rest", "scaling", "rotation", "opacity")))
+
+    _PLY_PROPS = (["x", "y", "z", "nx", "ny", "nz", "f_dc_0", "f_dc_1", "f_dc_2", "opacity", "scale_0", "scale_1",
+                   "scale_2", "rot_0", "rot_1", "rot_2", "rot_3"] + [f"f_rest_{i}" for i in range(45)])
+
+    def export_ply(self, path: str) -> None:
+        """export.py:53-139 — binary little-endian PLY, one ``vertex`` element of 62 float32 properties per
+        Gaussian in the reference's order: position, zero normal, ``features_dc`` (3), opacity logit, log-scales (3),
+        quaternion (4), then ``features_rest.reshape(N, 45)`` (coefficient-major, channel innermost — the reference's
+        own flattening, export.py:33-42).  The header is what ``plyfile`` writes for that structured array."""
+        import numpy as np
+        n = self._n
+        with torch.no_grad():
+            rows = torch.cat([self.xyz, torch.zeros_like(self.xyz), self.features[:, 0, :], self.opacity, self.scaling,
+                              self.rotation, self.features[:, 1:, :].reshape(n, 45)], dim=1)
+        data = np.ascontiguousarray(rows.to(torch.float32).cpu().numpy().astype("<f4"))
+        header = ["ply", "format binary_little_endian 1.0", f"element vertex {n}"]
+        header += [f"property float {p}" for p in self._PLY_PROPS] + ["end_header"]
+        with open(path, "wb") as f:
+            f.write(("\n".join(header) + "\n").encode("ascii"))
+            f.write(data.tobytes())
+
+    @classmethod
+    def from_ply(cls, path: str, device: str = "cuda") -> "GaussianStore":
+        """Inverse of :meth:`export_ply` (also reads files without the optional ``f_rest_*`` block)."""
+        import numpy as np
+        with open(path, "rb") as f:
+            if f.readline().strip() != b"ply":
+                raise ValueError("not a PLY file")
+            props, n = [], None
+            while True:
+                line = f.readline()
+                if not line:
+                    raise ValueError("PLY header has no end_header")
+                tok = line.decode("ascii").split()
+                if tok[:1] == ["format"] and tok[1] != "binary_little_endian":
+                    raise ValueError(f"unsupported PLY format {tok[1]}")
+                if tok[:2] == ["element", "vertex"]:
+                    n = int(tok[2])
+                elif tok[:1] == ["property"]:
+                    if tok[1] not in ("float", "float32"):
+                        raise ValueError(f"unsupported PLY property type {tok[1]}")
+                    props.append(tok[2])
+                elif tok[:1] == ["end_header"]:
+                    break
+            if n is None:
+                raise ValueError("PLY file has no vertex element")
+            raw = np.frombuffer(f.read(n * len(props) * 4), dtype="<f4")
+        if raw.size != n * len(props):
+            raise ValueError("PLY vertex data is truncated")
+        t = torch.from_numpy(raw.reshape(n, len(props)).copy())
+        col = {p: i for i, p in enumerate(props)}
+        take = lambda names: t[:, [col[p] for p in names]]  # noqa: E731
+        rest = take([f"f_rest_{i}" for i in range(45)]) if "f_rest_0" in col else torch.zeros(n, 45)
+        return cls.from_tensors(take(["x", "y", "z"]).to(device), take(["f_dc_0", "f_dc_1", "f_dc_2"]).to(device),
+                                rest.to(device), take(["scale_0", "scale_1", "scale_2"]).to(device),
+                                take(["rot_0", "rot_1", "rot_2", "rot_3"]).to(device), take(["opacity"]).to(device))

@@ -14,6 +14,7 @@ from __future__ import annotations
 import argparse
 import importlib
 import json
+import math
 import os
 import subprocess
 import sys
@@ -302,7 +303,8 @@ def run_b200(args):
     # memory (prefetched), GaussianStore.render, fused L1+SSIM loss (mean over views), backward with in-kernel gradient
     # accumulation, [all-reduce], one-kernel Adam, densification statistic; the loss is read back once per step
     ref_lrs = {"xyz": 1.6e-4, "f_dc": 0.0025, "f_rest": 0.0025 / 20.0, "opacity": 0.05, "scaling": 0.005, "rotation": 0.001}
-    adam = pkg.StoreAdam(store, ref_lrs)
+    # trainer.py:854-859 caps the log-scales every iteration at log(scene_extent * scale_clamp_ratio): folded into Adam
+    adam = pkg.StoreAdam(store, ref_lrs, scale_ceiling=math.log(10.0 * 0.2 + 1e-9))
     train_state = {"k": 0, "primed": False}
 
     def step_train(step):

@@ -215,9 +215,12 @@ int b200_l1_ssim_fwd_bwd(const float* render, const float* gt, int width, int he
 /* ---- f4: the optimiser step over the flat parameter store -----------------------
  * torch.optim.Adam semantics (trainer.py:331-340: six groups, eps 1e-15; no amsgrad / weight decay) in one
  * pass over params / grads / exp_avg / exp_avg_sq of identical flat layout (n_floats, multiple of 4, 16-B
- * aligned).  seg_host: n_seg (<= 8) rows of six doubles {begin, end, lr, lr_alt, period, split}: elements
- * [begin,end) use lr, except where period > 0 and (i - begin) % period >= split, which use lr_alt (the
- * features_dc / features_rest rates inside the [N,16,3] SH block: period 48, split 3).  step = Adam's t >= 1. */
+ * aligned).  seg_host: n_seg (<= 8) rows of B200_ADAM_SEG_DOUBLES doubles {begin, end, lr, lr_alt, period, split,
+ * clamp_max}: elements [begin,end) use lr, except where period > 0 and (i - begin) % period >= split, which use
+ * lr_alt (the features_dc / features_rest rates inside the [N,16,3] SH block: period 48, split 3); the updated
+ * parameter is min(p, clamp_max) — +inf for none — which is the reference's per-iteration cap on the log-scales
+ * (scaling.data.clamp_(max=scale_ceiling), trainer.py:854-859) folded into the same pass.  step = Adam's t >= 1. */
+#define B200_ADAM_SEG_DOUBLES 7
 int b200_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n_floats,
                    const double* seg_host, int n_seg, int step, float beta1, float beta2, float eps,
                    void* stream);

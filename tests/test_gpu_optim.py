@@ -38,3 +38,40 @@ def test_store_adam_matches_torch_adam(pkg, oracle, N):
             assert torch.allclose(q.detach(), p.detach(), rtol=1e-5, atol=3e-7), (it, k, (q - p).abs().max().item())
     pad = st.flat.numel() - 59 * N
     assert pad >= 0 and opt.t == 5
+
+
+def test_scale_ceiling_is_the_reference_clamp(pkg, oracle):
+    """trainer.py:854-859: `scaling.data.clamp_(max=scale_ceiling)` after every optimiser step, here folded into the
+    Adam kernel; every other block must be untouched by the bound."""
+    N = 5000
+    sc = oracle.synthetic_scene(N, 64, 48, seed=22)
+    raw = {k: sc[k].to(DEV).clone().requires_grad_(True)
+           for k in ("xyz", "features_dc", "features_rest", "opacity", "scaling", "rotation")}
+    groups = [{"params": [raw[k]], "lr": LRS[a]} for k, a in
+              (("xyz", "xyz"), ("features_dc", "f_dc"), ("features_rest", "f_rest"), ("opacity", "opacity"),
+               ("scaling", "scaling"), ("rotation", "rotation"))]
+    ref = torch.optim.Adam(groups, lr=0.0, eps=1e-15)
+    st = pkg.GaussianStore.from_tensors(sc["xyz"].to(DEV), sc["features_dc"].to(DEV), sc["features_rest"].to(DEV),
+                                        sc["scaling"].to(DEV), sc["rotation"].to(DEV), sc["opacity"].to(DEV))
+    ceiling = float(sc["scaling"].median())  # about half the log-scales sit above the cap
+    opt = pkg.StoreAdam(st, LRS, scale_ceiling=ceiling)
+    gen = torch.Generator().manual_seed(6)
+    for it in range(3):
+        st.zero_grad()
+        for k, p in raw.items():
+            g = torch.randn(p.shape, generator=gen).to(DEV)
+            p.grad = g.clone()
+            getattr(st, k).grad.copy_(g)
+        ref.step()
+        with torch.no_grad():
+            raw["scaling"].data.clamp_(max=ceiling)
+        opt.step()
+        assert st.scaling.max().item() <= ceiling
+        for k, p in raw.items():
+            q = getattr(st, k)
+            assert torch.allclose(q.detach(), p.detach(), rtol=1e-5, atol=3e-7), (it, k, (q - p).abs().max().item())
+    opt.scale_ceiling = None  # switching the bound off again
+    st.zero_grad()
+    st.scaling.grad.fill_(-1.0)
+    opt.step()
+    assert st.scaling.max().item() > ceiling

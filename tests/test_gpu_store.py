@@ -129,3 +129,51 @@ def test_store_layout_and_optimizer_groups(pkg, oracle):
     res = st.render(K, _viewpoint(sc, W, H), sh_degree=3)
     (res["render"] - gt).abs().mean().backward()
     assert st.xyz.grad is not None and st.xyz.grad.data_ptr() == st.flat_grad.data_ptr()
+
+
+def test_reset_opacity_matches_reference_expression(pkg, oracle):
+    """trainer.py:841-850."""
+    sc = _raw_scene(oracle, 4000, 64, 48, seed=9)
+    st = _store_from_scene(pkg, sc)
+    before = st.flat.clone()
+    cur = torch.sigmoid(sc["opacity"].to(DEV))
+    want = torch.logit(torch.minimum(cur, torch.full_like(cur, 0.01)).clamp(min=1e-6, max=1.0 - 1e-6))
+    st.reset_opacity()
+    assert torch.equal(st.opacity.detach(), want)
+    assert st.get_opacity.max().item() <= 0.01 + 1e-7
+    o = st._offsets["opacity"]
+    mask = torch.ones_like(before, dtype=torch.bool)
+    mask[o: o + len(st)] = False
+    assert torch.equal(st.flat[mask], before[mask])  # nothing else moved
+
+
+def test_ply_and_checkpoint_wire_format(pkg, oracle, tmp_path):
+    """export.py:53-139: 62 little-endian float32 per vertex in the reference's property order, under the header
+    plyfile writes; plus the reference's checkpoint keys (trainer.py:384-395) and the round trips."""
+    import numpy as np
+    N = 300
+    sc = _raw_scene(oracle, N, 64, 48, seed=10)
+    st = _store_from_scene(pkg, sc)
+    path = str(tmp_path / "checkpoint_7.ply")
+    st.export_ply(path)
+    blob = open(path, "rb").read()
+    names = (["x", "y", "z", "nx", "ny", "nz", "f_dc_0", "f_dc_1", "f_dc_2", "opacity", "scale_0", "scale_1", "scale_2",
+              "rot_0", "rot_1", "rot_2", "rot_3"] + [f"f_rest_{i}" for i in range(45)])
+    header = "ply\nformat binary_little_endian 1.0\nelement vertex %d\n" % N
+    header += "".join(f"property float {p}\n" for p in names) + "end_header\n"
+    assert blob[: len(header)] == header.encode("ascii")
+    # the body, built the way export.py builds it from a reference state dict: column blocks concatenated per vertex
+    sd = {k: v.cpu().numpy() for k, v in st.reference_state_dict().items()}
+    assert sd["features_dc"].shape == (N, 1, 3) and sd["features_rest"].shape == (N, 15, 3) and sd["opacity"].shape == (N, 1)
+    mat = np.concatenate([sd["xyz"], np.zeros((N, 3), np.float32), sd["features_dc"].reshape(N, -1)[:, :3],
+                          sd["opacity"].reshape(N, 1), sd["scaling"], sd["rotation"].reshape(N, 4),
+                          sd["features_rest"].reshape(N, -1)[:, :45]], axis=1).astype("<f4")
+    assert len(blob) == len(header) + N * 62 * 4
+    assert blob[len(header):] == mat.tobytes()
+    # round trips: PLY -> store and checkpoint dict -> store reproduce every float
+    back = pkg.GaussianStore.from_ply(path)
+    assert torch.equal(back.flat, st.flat)
+    again = pkg.GaussianStore.from_reference_state_dict({"iteration": 7, "model_state": st.reference_state_dict()})
+    assert torch.equal(again.flat, st.flat)
+    for k in ("xyz", "features_dc", "features_rest", "scaling", "rotation", "opacity"):
+        assert torch.equal(getattr(again, k).detach().cpu(), sc[k].reshape(getattr(again, k).shape))
