@@ -18,6 +18,17 @@ namespace {
 
 struct __align__(16) Pending { int id; float A, B, C; };
 
+#ifdef B200_TRACE_UNITS  // tuning aid (profiles/unit_trace.py): start / end time and SM of every work unit
+__device__ unsigned long long g_unit_trace[3 * 65536];
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+__device__ __forceinline__ unsigned smid() { unsigned r; asm volatile("mov.u32 %0, %%smid;" : "=r"(r)); return r; }
+#define TRACE_BEGIN() do { if (lane == 0 && unit < 65536) { g_unit_trace[3 * unit] = gtime(); g_unit_trace[3 * unit + 2] = smid(); } } while (0)
+#define TRACE_END() do { if (lane == 0 && unit < 65536) g_unit_trace[3 * unit + 1] = gtime(); } while (0)
+#else
+#define TRACE_BEGIN()
+#define TRACE_END()
+#endif
+
 // Reduction of RB_GROUP x 32 lanes x 12 partial sums through shared memory.  Lane (g, q, h) = (lane>>3,
 // (lane>>1)&3, lane&1) adds the float4 group q of Gaussian g over the 16 source lanes 2i+h — 16 LDS.128 +
 // 64 FADD for four Gaussians, one shuffle level to join the halves — and the 12 lanes with h == 0, q < 3 each
@@ -74,6 +85,7 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int unit = blockIdx.x * WARPS + wid;
     if (unit >= 2 * n_tiles) return;
+    TRACE_BEGIN();
     const int tile = unit >> 1, half = unit & 1;
     const int ty = tile / tile_w, tx = tile - ty * tile_w;
     const int lx = lane & 7, ly = lane >> 3;
@@ -117,7 +129,7 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
         warp_last = max(warp_last, bin_final[s]);
     }
     warp_last = __reduce_max_sync(0xffffffffu, warp_last);
-    if (warp_last < start) return;
+    if (warp_last < start) { TRACE_END(); return; }
     const float pxc = (float)(x_base + lx) + 4.5f, pyc = (float)(y_base + ly) + 2.5f;  // centroid of the 4 pixels
     const float bx0 = (float)x_base + 0.5f, bx1 = (float)min(x_base + 15, W - 1) + 0.5f;
     const float by0 = (float)y_base + 0.5f, by1 = (float)min(y_base + 7, H - 1) + 0.5f;
@@ -208,9 +220,17 @@ raster_bwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
         __syncwarp();
     }
     if (np) flush_pending(part, pend, np, lane, v_splats);
+    TRACE_END();
 }
 
 }  // namespace
+
+#ifdef B200_TRACE_UNITS
+extern "C" int b200_debug_unit_trace(unsigned long long* host_out, int n_units) {
+    cudaDeviceSynchronize();
+    return cudaMemcpyFromSymbol(host_out, g_unit_trace, sizeof(unsigned long long) * 3 * (size_t)n_units) == cudaSuccess ? 0 : 1;
+}
+#endif
 
 extern "C" int b200_raster_bwd(const float* splats, const int32_t* flatten_ids, const int32_t* offsets, int64_t M,
                                int width, int height, int channels, const float* background, int n_background,
