@@ -27,18 +27,26 @@
 
 namespace {
 
-// Lanes of `act` holding the same 8-bit digit.  Eight ballots pipeline back to back, whereas MATCH.ANY
-// serialises on the number of distinct values in the warp (measured: short-scoreboard stalls dominated
-// the first version of the ranking loop, profiles/ncu_r01_summary.md).
-__device__ __forceinline__ unsigned digit_peers(unsigned act, uint32_t d) {
-    unsigned peers = act;
+// Lanes holding the same BITS-bit digit, three instructions per bit after the predicates (ptxas packs those into
+// R2P): ballot, the lane's own bit widened to a mask (SELP), and ONE LOP3 folding "lanes that disagree with me in
+// this bit" into x (x |= vote ^ mask).  The earlier form (two predicated LOP3) compiled to LOP3+SEL pairs, five
+// ALU-pipe instructions per bit, and the ALU pipe (half rate) was what throttled the pass (math_pipe_throttle).
+template <int BITS>
+__device__ __forceinline__ unsigned digit_peers_n(uint32_t d) {
+    unsigned x = 0;
 #pragma unroll
-    for (int b = 0; b < RS_BITS; ++b) {
-        const bool bit = (d >> b) & 1u;
-        const unsigned vote = __ballot_sync(act, bit);
-        peers &= bit ? vote : ~vote;
+    for (int b = 0; b < BITS; ++b) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t.reg .b32 v, m, t;\n\t"
+            "and.b32 t, %1, %2;\n\t"
+            "setp.ne.u32 p, t, 0;\n\t"
+            "vote.sync.ballot.b32 v, p, 0xffffffff;\n\t"
+            "selp.b32 m, 0xffffffff, 0, p;\n\t"
+            "lop3.b32 %0, %0, v, m, 0xF6;\n\t}"
+            : "+r"(x)
+            : "r"(d), "r"(1u << b));
     }
-    return peers;
+    return ~x;
 }
 
 // All per-pass digit histograms in one read of the keys.  Each warp owns private histogram rows in
@@ -80,8 +88,8 @@ rs_hist_kernel(const KeyT* __restrict__ keys, int64_t n, int npasses, int end_bi
                 const int shift = p * RS_BITS;
                 const int bits = min(RS_BITS, end_bit - shift);
                 const uint32_t d = (uint32_t)((uint64_t)k[v] >> shift) & ((1u << bits) - 1u);
-                const unsigned peers = digit_peers(0xffffffffu, d) & vmask;
-                if (valid && (__ffs(peers) - 1) == lane) my_rows[p * RS_RADIX + d] += __popc(peers);
+                const unsigned peers = digit_peers_n<RS_BITS>(d) & vmask;
+                if (valid && (31 - __clz(peers)) == lane) my_rows[p * RS_RADIX + d] += __popc(peers);
                 __syncwarp();
             }
         }
@@ -124,26 +132,6 @@ struct __align__(16) RsSmem {
     uint32_t warp_scan[RS_WARPS];
     uint32_t tile;
 };
-
-// Lanes holding the same BITS-bit digit, four instructions per bit: predicate from the digit bit, ballot, and one
-// of two predicated LOP3 folding "lanes that disagree with me in this bit" into x (x |= bit ? ~vote : vote).
-template <int BITS>
-__device__ __forceinline__ unsigned digit_peers_n(uint32_t d) {
-    unsigned x = 0;
-#pragma unroll
-    for (int b = 0; b < BITS; ++b) {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t.reg .b32 v, t;\n\t"
-            "and.b32 t, %1, %2;\n\t"
-            "setp.ne.u32 p, t, 0;\n\t"
-            "vote.sync.ballot.b32 v, p, 0xffffffff;\n\t"
-            "@p lop3.b32 %0, %0, v, 0, 0xF3;\n\t"
-            "@!p lop3.b32 %0, %0, v, 0, 0xFC;\n\t}"
-            : "+r"(x)
-            : "r"(d), "r"(1u << b));
-    }
-    return ~x;
-}
 
 // One LSD pass.  dmask selects the digit bits of this pass, BITS >= popcount(dmask) is the number of ballots spent.  All indices are 32-bit
 // (n < 2^30); full tiles take an unpredicated path.
@@ -196,7 +184,7 @@ rs_onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict_
     for (int i = 0; i < RS_ITEMS; ++i) {
         const uint32_t d = (uint32_t)(key[i] >> shift) & dmask;
         const unsigned peers = digit_peers_n<BITS>(d);
-        const int leader = __ffs(peers) - 1;
+        const int leader = 31 - __clz(peers);  // any one lane of the group may update the row; the highest costs one FLO
         uint32_t base = 0;
         if (lane == leader) {
             base = my_row[d];
