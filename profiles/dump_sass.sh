@@ -15,6 +15,6 @@ dump raster_fwd.o 'raster_fwd_kernelILi0ELi4' raster_fwd_rgb.sass
 dump raster_bwd.o 'raster_bwd_kernelILi0ELi4' raster_bwd_rgb.sass
 dump project_sh.o 'project_sh_fwd_kernelILi3' project_sh_fwd_deg3.sass
 dump project_sh.o 'project_sh_bwd_kernelILi3' project_sh_bwd_deg3.sass
-dump radix_sort.o 'rs_onesweep_kernelItLb0' rs_onesweep_u16.sass
-dump radix_sort.o 'rs_onesweep_kernelIjLb0' rs_onesweep_u32.sass
+dump radix_sort.o 'rs_onesweep_kernelItLi8' rs_onesweep_u16.sass
+dump radix_sort.o 'rs_onesweep_kernelIjLi8' rs_onesweep_u32.sass
 dump binning.o 'bin_emit_sorted|tile_prep' binning_emit_prep.sass
