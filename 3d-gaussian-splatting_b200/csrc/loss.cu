@@ -122,18 +122,36 @@ l1_ssim_kernel(const float* __restrict__ render, const float* __restrict__ gt, i
         for (int w = 0; w < LOSS_THREADS / 32; ++w) t += s_red[tid][w];
         atomicAdd(sums + tid, t);
     }
+    // ---- the last CTA to arrive turns the three sums into (loss, l1, ssim, mse): no scalar kernels afterwards
+    __shared__ bool s_last;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned arrived = atomicAdd(reinterpret_cast<unsigned*>(sums + 3), 1u);
+        s_last = arrived == gridDim.x * gridDim.y - 1;
+    }
+    __syncthreads();
+    if (s_last && tid == 0) {
+        __threadfence();
+        const float l1 = __ldcg(sums + 0) * n_inv, ssim = __ldcg(sums + 1) * n_inv, mse = __ldcg(sums + 2) * n_inv;
+        sums[4] = (1.f - lambda) * l1 + lambda * (1.f - ssim);
+        sums[5] = l1;
+        sums[6] = ssim;
+        sums[7] = mse;
+    }
 }
 
 }  // namespace
 
-// render[H,W,3], gt[H,W,3] -> sums[3] = (sum |x-gt|, sum of window SSIMs, sum (x-gt)^2) over 3*H*W elements
-// (cleared by this call) and, if v_render != NULL, v_render[H,W,3] = grad_scale * d loss / d render with
-// loss = (1-lambda) * sums[0]/n + lambda * (1 - sums[1]/n), n = 3*H*W.
+// render[H,W,3], gt[H,W,3] -> sums[8]: [0..2] = (sum |x-gt|, sum of window SSIMs, sum (x-gt)^2) over n = 3*H*W
+// elements, [3] = arrival counter (both cleared by this call), [4..7] = (loss, l1, ssim, mse) with
+// loss = (1-lambda) * sums[0]/n + lambda * (1 - sums[1]/n), written by the last CTA; and, if v_render != NULL,
+// v_render[H,W,3] = grad_scale * d loss / d render.
 extern "C" int b200_l1_ssim_fwd_bwd(const float* render, const float* gt, int width, int height, float lambda_dssim,
                                     float grad_scale, float* v_render, float* sums, void* stream) {
     B200_REQUIRE(width > 0 && height > 0 && render && gt && sums, "bad argument");
     cudaStream_t st = (cudaStream_t)stream;
-    cudaMemsetAsync(sums, 0, 3 * sizeof(float), st);
+    cudaMemsetAsync(sums, 0, 4 * sizeof(float), st);
     dim3 grid((width + LT_X - 1) / LT_X, (height + LT_Y - 1) / LT_Y);
     l1_ssim_kernel<<<grid, LOSS_THREADS, 0, st>>>(render, gt, width, height, lambda_dssim, grad_scale, v_render, sums);
     return b200_check_launch("l1_ssim_fwd_bwd");

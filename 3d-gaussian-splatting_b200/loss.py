@@ -27,13 +27,12 @@ class _L1SSIM(torch.autograd.Function):
         H, W = render.shape[0], render.shape[1]
         need_grad = ctx.needs_input_grad[0]
         v_render = torch.empty_like(render) if need_grad else None
-        sums = torch.empty(3, dtype=torch.float32, device=render.device)
+        sums = torch.empty(8, dtype=torch.float32, device=render.device)  # 3 sums, counter, (loss, l1, ssim, mse)
         with torch.cuda.device(render.device):
             check(lib.b200_l1_ssim_fwd_bwd(render.data_ptr(), gt.data_ptr(), W, H, float(lambda_dssim), 1.0,
                                            None if v_render is None else v_render.data_ptr(), sums.data_ptr(),
                                            torch.cuda.current_stream().cuda_stream), "b200_l1_ssim_fwd_bwd")
-        stats = sums / float(3 * H * W)  # (l1, ssim, mse of the clamped render)
-        loss = (1.0 - lambda_dssim) * stats[0] + lambda_dssim * (1.0 - stats[1])
+        loss, stats = sums[4], sums[5:8]  # finished by the kernel's last CTA: (l1, ssim, mse of the clamped render)
         ctx.v_render = v_render
         ctx.mark_non_differentiable(stats)
         return loss, stats

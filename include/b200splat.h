@@ -207,8 +207,9 @@ int b200_densify_stats(const float* xyz_grad, int64_t N, float* accum, float* co
 /* ---- f3: the reference's per-view photometric loss, forward + gradient fused ----
  * trainer.py:485-492: x = clamp(render,0,1) (straight-through), loss = (1-lambda) mean|x-gt| +
  * lambda (1 - SSIM_3x3box(x, gt)) (_compute_ssim, trainer.py:354-371).  render/gt are [H,W,3].
- * sums[3] (cleared by the call) receive sum|x-gt|, the sum of window SSIMs and sum (x-gt)^2 over the
- * n = 3*H*W elements; v_render (optional) receives grad_scale * d loss / d render. */
+ * sums[8]: [0..2] receive sum|x-gt|, the sum of window SSIMs and sum (x-gt)^2 over the n = 3*H*W elements,
+ * [3] is an arrival counter (both cleared by the call), [4..7] = (loss, l1, ssim, mse) finished by the last
+ * CTA, so that the step needs no scalar kernels; v_render (optional) receives grad_scale * d loss / d render. */
 int b200_l1_ssim_fwd_bwd(const float* render, const float* gt, int width, int height,
                          float lambda_dssim, float grad_scale, float* v_render, float* sums, void* stream);
 
