@@ -12,9 +12,10 @@ from .stats import densify_stats  # noqa: F401
 from .store import GaussianStore  # noqa: F401
 from .loss import l1_ssim_loss  # noqa: F401
 from .optim import StoreAdam  # noqa: F401
-from .distributed import shard_views, allreduce_gradients, ViewShardedStep  # noqa: F401
+from .streams import ViewStreams  # noqa: F401
+from .distributed import shard_views, allreduce_gradients, allreduce_flat, ViewShardedStep  # noqa: F401
 
 __all__ = [
     "rasterization", "project_and_bin", "RasterizeSplats", "make_cam", "B200Backend", "densify_stats", "GaussianStore", "l1_ssim_loss", "StoreAdam",
-    "shard_views", "allreduce_gradients", "ViewShardedStep",
+    "ViewStreams", "shard_views", "allreduce_gradients", "allreduce_flat", "ViewShardedStep",
 ]

@@ -7,11 +7,19 @@
 
 #define PROJ_THREADS 256
 
-// The camera block lives in constant memory (bank-addressed operands, no registers).  It is refreshed by a
-// stream-ordered copy in front of every projection launch — from the caller's packed DEVICE block
-// (b200_cam_pack; the pose never visits the host) or from a host block.  One slot: launches on a different
-// stream first wait for the last kernel that read it (load_cam / cam_used below).
-__constant__ Cam c_cam;
+// The camera block is read from DEVICE memory (the caller's packed block, b200_cam_pack: the pose never visits the
+// host) and staged once per CTA in shared memory.  No global slot is shared between launches, so projection kernels
+// of different views may be in flight on different streams at the same time (streams.ViewStreams).  A HOST camera
+// block is first copied into c_cam_staging, which is one slot: such launches on a different stream wait for the
+// last kernel that read it (load_cam / cam_used below).
+__device__ Cam c_cam_staging;
+
+#define STAGE_CAM(cam_g)                                                                                           \
+    __shared__ Cam s_cam;                                                                                          \
+    if (threadIdx.x < sizeof(Cam) / 4)                                                                             \
+        reinterpret_cast<uint32_t*>(&s_cam)[threadIdx.x] = __ldg(reinterpret_cast<const uint32_t*>(cam_g) + threadIdx.x); \
+    __syncthreads();                                                                                               \
+    const Cam& cam = s_cam
 
 namespace {
 
@@ -165,6 +173,9 @@ __device__ __forceinline__ void load_sh(const float* __restrict__ shs, int64_t g
 // RAW: the inputs are the reference's raw parameters (gaussian_model.py:65-76) and the getters' activations
 // (gaussian_model.py:90-108: exp / sigmoid; F.normalize is the quaternion normalisation done here anyway) are
 // applied in registers — no activated copies of the parameter store are ever materialised.
+#ifndef PROJ_PREFETCH_SH
+#define PROJ_PREFETCH_SH 0
+#endif
 template <int DEG, bool RAW>
 __global__ void __launch_bounds__(PROJ_THREADS)
 project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__ quats,
@@ -173,10 +184,27 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
                       int32_t* __restrict__ radii, float* __restrict__ splats,
                       int32_t* __restrict__ tiles_per_gauss, int64_t* __restrict__ block_sums,
                       uint32_t* __restrict__ depth_keys, int32_t* __restrict__ gauss_ids,
-                      int32_t* __restrict__ tile_grid) {
-    const Cam& cam = c_cam;
+                      int32_t* __restrict__ tile_grid, const Cam* __restrict__ cam_g) {
+    STAGE_CAM(cam_g);
     int64_t g = (int64_t)blockIdx.x * PROJ_THREADS + threadIdx.x;
     int ntiles = 0;
+#if PROJ_PREFETCH_SH == 1
+    // The SH rows of a warp's 32 Gaussians are one contiguous run (32 x 12 x (DEG+1)^2 bytes of each 16-coefficient
+    // row, rows back to back).  They are only read after the cull decision, i.e. after a first round trip for the
+    // position / scale / rotation: one bulk L2 prefetch per warp (TMA, no destination) overlaps the two latencies.
+    if (DEG >= 0 && vec_ok && (threadIdx.x & 31) == 0 && g < N) {
+        const int64_t rows = (N - g) < 32 ? (N - g) : 32;
+        const uint32_t bytes = (uint32_t)(rows * sh_coeffs * 12);
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(shs + g * (int64_t)sh_coeffs * 3), "r"(bytes) : "memory");
+    }
+#elif PROJ_PREFETCH_SH == 2
+    if (DEG >= 0 && g < N) {
+        const char* row = reinterpret_cast<const char*>(shs + g * (int64_t)sh_coeffs * 3);
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(row));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(row + 64));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(row + 128));
+    }
+#endif
     if (g < N) {
         float px = __ldg(means + 3 * g), py = __ldg(means + 3 * g + 1), pz = __ldg(means + 3 * g + 2);
         float4 q = __ldg(reinterpret_cast<const float4*>(quats) + g);
@@ -318,8 +346,8 @@ project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__
                       const float* __restrict__ shs, int sh_coeffs, bool vec_ok, int64_t N,
                       const int32_t* __restrict__ radii, const float* __restrict__ v_splats,
                       float* __restrict__ v_means, float* __restrict__ v_quats, float* __restrict__ v_scales,
-                      float* __restrict__ v_opacities, float* __restrict__ v_shs) {
-    const Cam& cam = c_cam;
+                      float* __restrict__ v_opacities, float* __restrict__ v_shs, const Cam* __restrict__ cam_g) {
+    STAGE_CAM(cam_g);
     constexpr bool RAW = MODE != 0, ACC = MODE == 2;
     constexpr int D = DEG < 0 ? 0 : DEG;
     constexpr int NB = ShCount<D>::NB;
@@ -541,28 +569,32 @@ cudaEvent_t g_cam_event[CAM_MAX_DEV];
 cudaStream_t g_cam_stream[CAM_MAX_DEV];
 bool g_cam_event_ok[CAM_MAX_DEV];
 
-// Stream-ordered refresh of c_cam.  Returns the device ordinal (for cam_used) or a negative error code.
-int load_cam(const float* cam_host, const float* cam_dev, int W, int H, cudaStream_t st) {
+// Device address of the camera block the next projection launch on `st` reads: the caller's device block as is,
+// or the staging slot after a stream-ordered upload of a host block.  `*slot_dev` receives the device ordinal when
+// the staging slot is in use (for cam_used), else -1.  Returns nullptr after recording an error.
+const Cam* load_cam(const float* cam_host, const float* cam_dev, int W, int H, cudaStream_t st, int* slot_dev) {
+    *slot_dev = -1;
+    if (cam_dev) return reinterpret_cast<const Cam*>(cam_dev);
     int dev = 0;
     cudaGetDevice(&dev);
-    if (dev < 0 || dev >= CAM_MAX_DEV) { b200_set_error("device ordinal %d out of range", dev); return B200_EARG; }
+    if (dev < 0 || dev >= CAM_MAX_DEV) { b200_set_error("device ordinal %d out of range", dev); return nullptr; }
     if (!g_cam_event_ok[dev]) {
-        if (cudaEventCreateWithFlags(&g_cam_event[dev], cudaEventDisableTiming) != cudaSuccess) return b200_check_launch("cam event");
+        if (cudaEventCreateWithFlags(&g_cam_event[dev], cudaEventDisableTiming) != cudaSuccess) { b200_check_launch("cam event"); return nullptr; }
         g_cam_event_ok[dev] = true;
         g_cam_stream[dev] = st;
     } else if (g_cam_stream[dev] != st) {
-        cudaStreamWaitEvent(st, g_cam_event[dev], 0);  // the previous reader of c_cam ran on another stream
+        cudaStreamWaitEvent(st, g_cam_event[dev], 0);  // the previous reader of the staging slot ran on another stream
     }
-    if (cam_dev) {
-        cudaMemcpyToSymbolAsync(c_cam, cam_dev, sizeof(Cam), 0, cudaMemcpyDeviceToDevice, st);
-    } else {
-        Cam cam = b200_make_cam(cam_host, W, H);
-        cudaMemcpyToSymbolAsync(c_cam, &cam, sizeof(Cam), 0, cudaMemcpyHostToDevice, st);
-    }
-    return dev;
+    Cam cam = b200_make_cam(cam_host, W, H);
+    cudaMemcpyToSymbolAsync(c_cam_staging, &cam, sizeof(Cam), 0, cudaMemcpyHostToDevice, st);
+    void* addr = nullptr;
+    if (cudaGetSymbolAddress(&addr, c_cam_staging) != cudaSuccess) { b200_check_launch("cam staging address"); return nullptr; }
+    *slot_dev = dev;
+    return reinterpret_cast<const Cam*>(addr);
 }
 
 void cam_used(int dev, cudaStream_t st) {
+    if (dev < 0) return;
     cudaEventRecord(g_cam_event[dev], st);
     g_cam_stream[dev] = st;
 }
@@ -606,10 +638,11 @@ static int project_fwd_impl(bool raw, const float* means, const float* quats, co
     bool vec_ok = sh_degree >= 0 && ((sh_coeffs * 12) % 16 == 0) && (((uintptr_t)shs & 15) == 0);
     dim3 grid((unsigned)b200_project_blocks(N)), block(PROJ_THREADS);
     cudaStream_t st = (cudaStream_t)stream;
-    const int cdev = load_cam(cam_host, cam_dev, width, height, st);
-    if (cdev < 0) return cdev;
-#define LAUNCH(D) do { if (raw) project_sh_fwd_kernel<D, true><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid); \
-                       else project_sh_fwd_kernel<D, false><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid); } while (0)
+    int cdev = -1;
+    const Cam* cam_g = load_cam(cam_host, cam_dev, width, height, st, &cdev);
+    if (cam_g == nullptr) return B200_ECUDA;
+#define LAUNCH(D) do { if (raw) project_sh_fwd_kernel<D, true><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, cam_g); \
+                       else project_sh_fwd_kernel<D, false><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, cam_g); } while (0)
     switch (sh_degree) {
         case 0: LAUNCH(0); break;
         case 1: LAUNCH(1); break;
@@ -654,9 +687,10 @@ static int project_bwd_impl(int mode, const float* means, const float* quats, co
     bool vec_ok = sh_degree >= 0 && ((sh_coeffs * 12) % 16 == 0) && (((uintptr_t)shs & 15) == 0) && (((uintptr_t)v_shs & 15) == 0);
     dim3 grid((unsigned)b200_project_blocks(N)), block(PROJ_THREADS);
     cudaStream_t st = (cudaStream_t)stream;
-    const int cdev = load_cam(cam_host, cam_dev, width, height, st);
-    if (cdev < 0) return cdev;
-#define ARGS means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, v_splats, v_means, v_quats, v_scales, v_opacities, v_shs
+    int cdev = -1;
+    const Cam* cam_g = load_cam(cam_host, cam_dev, width, height, st, &cdev);
+    if (cam_g == nullptr) return B200_ECUDA;
+#define ARGS means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, v_splats, v_means, v_quats, v_scales, v_opacities, v_shs, cam_g
 #define LAUNCH(D) do { if (mode == 0) project_sh_bwd_kernel<D, 0><<<grid, block, 0, st>>>(ARGS); \
                        else if (mode == 1) project_sh_bwd_kernel<D, 1><<<grid, block, 0, st>>>(ARGS); \
                        else project_sh_bwd_kernel<D, 2><<<grid, block, 0, st>>>(ARGS); } while (0)

@@ -3,6 +3,9 @@
 #include <stdlib.h>
 #include "raster_common.cuh"
 
+#ifndef RF_VARIANT
+#define RF_VARIANT 1
+#endif
 #ifndef RF_MIN_WARPS
 #define RF_MIN_WARPS 32  // resident warps per SM the register allocation must allow
 #endif
@@ -79,18 +82,31 @@ raster_fwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
             const int idx = stage[j].idx;
 #pragma unroll
             for (int s = 0; s < RU_SLOTS; ++s) {
-                if (ok[s]) {  // a slot no lane reaches is one untaken branch
+#if RF_VARIANT == 2  // branch-free: every slot pays 12 instructions
+                {
                     const float Tn = T[s] * (1.f - al[s]);
-                    if (Tn <= T_STOP) {
-                        thr[s] = INF;
-                    } else {
-                        const float w = al[s] * T[s];
-                        if (HAS_RGB) { acc[s][0] += w * col.x; acc[s][1] += w * col.y; acc[s][2] += w * col.z; }
-                        if (HAS_D) acc[s][CH - 1] += w * col.w;
-                        last[s] = idx;
-                        T[s] = Tn;
-                    }
+                    const bool live = ok[s] && !(Tn <= T_STOP);
+                    const float w = live ? al[s] * T[s] : 0.f;
+                    thr[s] = (ok[s] && !live) ? INF : thr[s];
+                    if (HAS_RGB) { acc[s][0] = fmaf(w, col.x, acc[s][0]); acc[s][1] = fmaf(w, col.y, acc[s][1]); acc[s][2] = fmaf(w, col.z, acc[s][2]); }
+                    if (HAS_D) acc[s][CH - 1] = fmaf(w, col.w, acc[s][CH - 1]);
+                    last[s] = live ? idx : last[s];
+                    T[s] = live ? Tn : T[s];
                 }
+#else
+                if (ok[s]) {  // a slot no lane reaches is one untaken branch
+                    // selects, not an if/else: ptxas turned the two-way form into predicated moves with three
+                    // extra MOVs per slot; a pixel that finishes here takes w = 0 and raises its threshold to +inf
+                    const float Tn = T[s] * (1.f - al[s]);
+                    const bool live = !(Tn <= T_STOP);
+                    const float w = live ? al[s] * T[s] : 0.f;
+                    thr[s] = live ? thr[s] : INF;
+                    if (HAS_RGB) { acc[s][0] = fmaf(w, col.x, acc[s][0]); acc[s][1] = fmaf(w, col.y, acc[s][1]); acc[s][2] = fmaf(w, col.z, acc[s][2]); }
+                    if (HAS_D) acc[s][CH - 1] = fmaf(w, col.w, acc[s][CH - 1]);
+                    last[s] = live ? idx : last[s];
+                    T[s] = live ? Tn : T[s];
+                }
+#endif
             }
         }
         __syncwarp();

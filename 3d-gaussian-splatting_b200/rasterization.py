@@ -247,6 +247,9 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
     return out
 
 
+_ACC_EVENTS = {}  # (device, gradient-buffer address) -> event after the last in-place accumulation into it
+
+
 class RasterizeSplats(torch.autograd.Function):
     """forward = stages 1-3, backward = stages 4a-4b (gsplat's autograd of rasterization())."""
 
@@ -322,6 +325,14 @@ class RasterizeSplats(torch.autograd.Function):
                 v_scales = torch.empty_like(scales)
                 v_opac = torch.empty_like(opacities)
                 v_colors = torch.empty_like(colors)
+            acc_key = None
+            if grad_into is not None:
+                # the in-place "+=" of the accumulate mode is not atomic: views in flight on different streams
+                # (streams.ViewStreams) take turns on the gradient buffer
+                acc_key = (dev.index, v_means.data_ptr())
+                prev = _ACC_EVENTS.get(acc_key)
+                if prev is not None:
+                    torch.cuda.current_stream().wait_event(prev)
             with _stage("project_sh_bwd"):
                 if raw:
                     check(lib.b200_project_sh_bwd_raw(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities),
@@ -335,6 +346,12 @@ class RasterizeSplats(torch.autograd.Function):
                                                   _ptr(v_splats), _ptr(v_means), _ptr(v_quats), _ptr(v_scales), _ptr(v_opac),
                                                   _ptr(v_colors), st), "b200_project_sh_bwd")
         if grad_into is not None:
+            if len(_ACC_EVENTS) > 64:
+                _ACC_EVENTS.clear()
+            ev = _ACC_EVENTS.get(acc_key) or torch.cuda.Event()
+            with torch.cuda.device(dev):
+                ev.record()
+            _ACC_EVENTS[acc_key] = ev
             return (None,) * 15
         return v_means, v_quats, v_scales, v_opac, v_colors, None, None, None, None, None, None, None, None, None, None
 

@@ -221,6 +221,8 @@ def run_b200(args):
     params_list = [leaves[k] for k in ("means3D", "scales", "rotations", "opacities", "shs")]
     flat = None
 
+    vstreams = pkg.ViewStreams(dev, args.view_streams, params_list)
+
     def view_index(step, v):
         return (step * world * V + rank * V + v) % 64
 
@@ -229,10 +231,13 @@ def run_b200(args):
         nonlocal flat
         for p in params_list:
             p.grad = None
+        vstreams.begin()
         for v in range(V):
-            vp = {"world_view_transform": poses_dev[view_index(step, v)], "image_width": W, "image_height": H}
-            res = backend.render_with_depth(leaves, vp, bg_color=bg, render_mode="RGB", device="cuda", sh_degree=deg)
-            res["render"].backward(v_render)
+            with vstreams.view(v):
+                vp = {"world_view_transform": poses_dev[view_index(step, v)], "image_width": W, "image_height": H}
+                res = backend.render_with_depth(leaves, vp, bg_color=bg, render_mode="RGB", device="cuda", sh_degree=deg)
+                res["render"].backward(v_render)
+        vstreams.join()
         if world > 1:
             flat = pkg.allreduce_gradients(params_list, world * V, flat=flat)
 
@@ -291,13 +296,15 @@ def run_b200(args):
 
     def step_store(step):
         store.zero_grad()
+        vstreams.begin()
         for v in range(V):
-            vp = {"world_view_transform": poses_dev[view_index(step, v)], "image_width": W, "image_height": H}
-            res = store.render(K, vp, bg_color=bg, render_mode="RGB", sh_degree=deg)
-            res["render"].backward(v_render)
+            with vstreams.view(v):
+                vp = {"world_view_transform": poses_dev[view_index(step, v)], "image_width": W, "image_height": H}
+                res = store.render(K, vp, bg_color=bg, render_mode="RGB", sh_degree=deg)
+                res["render"].backward(v_render)
+        vstreams.join()
         if world > 1:
-            dist.all_reduce(store.flat_grad)
-            store.flat_grad.mul_(1.0 / (world * V))
+            pkg.allreduce_flat(store.flat_grad, 1.0 / (world * V))
 
     # f1+f3+f4: one optimiser iteration as trainer.py:447-519 runs it, on the widened path — V views from pinned host
     # memory (prefetched), GaussianStore.render, fused L1+SSIM loss (mean over views), backward with in-kernel gradient
@@ -330,8 +337,7 @@ def run_b200(args):
             tot = tot + loss.detach()
             train_state["k"] = k + 1
         if world > 1:
-            dist.all_reduce(store.flat_grad)
-            store.flat_grad.mul_(1.0 / world)
+            pkg.allreduce_flat(store.flat_grad, 1.0 / world)
         adam.step()
         pkg.densify_stats(store.xyz_gradient_accum, store.xyz_gradient_count, store.xyz.grad)
         return float(tot.item())
@@ -491,6 +497,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", default="A", choices=sorted(CONFIGS))
     ap.add_argument("--views-per-rank", type=int, default=4)
+    ap.add_argument("--view-streams", type=int, default=1,
+                    help="CUDA streams the views of a step alternate over (ViewStreams); 1 = one stream")
     ap.add_argument("--total-views", type=int, default=0,
                     help="fixed number of views per step split over the ranks (strong scaling, config B: 64); "
                          "default 0 = --views-per-rank views on every rank (weak scaling)")

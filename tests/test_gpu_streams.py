@@ -1,0 +1,84 @@
+"""Views of one batch on alternating CUDA streams (3d-gaussian-splatting_b200/streams.py).
+
+The reference renders the views of a step one after the other (src/training/trainer.py:458-500); summed gradients do
+not depend on the order or on the overlap, so the two-stream schedule must reproduce the one-stream gradients — through
+the drop-in backend (autograd accumulates the per-view gradients) and through the store (the kernels add in place),
+repeated so that a race between views would show up as run-to-run differences."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _close(a, b, tol=2e-4):
+    scale = max(b.abs().max().item(), 1e-12)
+    return (a - b).abs().max().item() <= tol * scale
+
+
+def _views(oracle, sc, W, H, n):
+    cams = oracle.circle_cameras(64)
+    return [{"world_view_transform": cams[(7 * i) % 64].to(DEV), "image_width": W, "image_height": H} for i in range(n)]
+
+
+@pytest.mark.parametrize("n_streams", [2, 3])
+def test_dropin_backend_two_streams_same_gradients(pkg, oracle, n_streams):
+    N, W, H, V = 60000, 480, 270, 6
+    sc = oracle.synthetic_scene(N, W, H, seed=3)
+    act = oracle.activate(sc)
+    names = ("means3D", "scales", "rotations", "opacities", "shs")
+    leaves = {k: act[k].to(DEV).clone().requires_grad_(True) for k in names}
+    be = pkg.B200Backend(sc["K"].to(DEV))
+    bg = torch.zeros(3, device=DEV)
+    v = torch.randn(H, W, 3, generator=torch.Generator().manual_seed(5)).to(DEV)
+    views = _views(oracle, sc, W, H, V)
+
+    def step(vs):
+        for p in leaves.values():
+            p.grad = None
+        vs.begin()
+        imgs = []
+        for i, vp in enumerate(views):
+            with vs.view(i):
+                res = be.render_with_depth(leaves, vp, bg_color=bg, render_mode="RGB", device="cuda", sh_degree=3)
+                res["render"].backward(v)
+                imgs.append(res["render"].detach())
+        vs.join()
+        torch.cuda.synchronize()
+        return imgs, {k: leaves[k].grad.clone() for k in names}
+
+    imgs1, g1 = step(pkg.ViewStreams(DEV, 1))
+    vs = pkg.ViewStreams(DEV, n_streams, list(leaves.values()))
+    for rep in range(4):
+        imgs2, g2 = step(vs)
+        for a, b in zip(imgs1, imgs2):
+            assert torch.equal(a, b), "a view's image changed under the multi-stream schedule"
+        for k in names:
+            assert _close(g2[k], g1[k]), (k, rep)
+
+
+def test_store_two_streams_same_gradients(pkg, oracle):
+    N, W, H, V = 60000, 480, 270, 6
+    sc = oracle.synthetic_scene(N, W, H, seed=6)
+    st = pkg.GaussianStore.from_tensors(sc["xyz"].to(DEV), sc["features_dc"].to(DEV), sc["features_rest"].to(DEV),
+                                        sc["scaling"].to(DEV), sc["rotation"].to(DEV), sc["opacity"].to(DEV))
+    K = sc["K"].to(DEV)
+    bg = torch.zeros(3, device=DEV)
+    v = torch.randn(H, W, 3, generator=torch.Generator().manual_seed(8)).to(DEV)
+    views = _views(oracle, sc, W, H, V)
+
+    def step(vs):
+        st.zero_grad()
+        vs.begin()
+        for i, vp in enumerate(views):
+            with vs.view(i):
+                st.render(K, vp, bg_color=bg, render_mode="RGB", sh_degree=3)["render"].backward(v)
+        vs.join()
+        torch.cuda.synchronize()
+        return st.flat_grad.clone()
+
+    g1 = step(pkg.ViewStreams(DEV, 1))
+    assert g1.abs().max().item() > 0
+    vs = pkg.ViewStreams(DEV, 2)
+    for rep in range(4):
+        assert _close(step(vs), g1), rep
