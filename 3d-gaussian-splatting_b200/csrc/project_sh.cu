@@ -173,9 +173,6 @@ __device__ __forceinline__ void load_sh(const float* __restrict__ shs, int64_t g
 // RAW: the inputs are the reference's raw parameters (gaussian_model.py:65-76) and the getters' activations
 // (gaussian_model.py:90-108: exp / sigmoid; F.normalize is the quaternion normalisation done here anyway) are
 // applied in registers — no activated copies of the parameter store are ever materialised.
-#ifndef PROJ_PREFETCH_SH
-#define PROJ_PREFETCH_SH 0
-#endif
 template <int DEG, bool RAW>
 __global__ void __launch_bounds__(PROJ_THREADS)
 project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__ quats,
@@ -188,23 +185,6 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
     STAGE_CAM(cam_g);
     int64_t g = (int64_t)blockIdx.x * PROJ_THREADS + threadIdx.x;
     int ntiles = 0;
-#if PROJ_PREFETCH_SH == 1
-    // The SH rows of a warp's 32 Gaussians are one contiguous run (32 x 12 x (DEG+1)^2 bytes of each 16-coefficient
-    // row, rows back to back).  They are only read after the cull decision, i.e. after a first round trip for the
-    // position / scale / rotation: one bulk L2 prefetch per warp (TMA, no destination) overlaps the two latencies.
-    if (DEG >= 0 && vec_ok && (threadIdx.x & 31) == 0 && g < N) {
-        const int64_t rows = (N - g) < 32 ? (N - g) : 32;
-        const uint32_t bytes = (uint32_t)(rows * sh_coeffs * 12);
-        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(shs + g * (int64_t)sh_coeffs * 3), "r"(bytes) : "memory");
-    }
-#elif PROJ_PREFETCH_SH == 2
-    if (DEG >= 0 && g < N) {
-        const char* row = reinterpret_cast<const char*>(shs + g * (int64_t)sh_coeffs * 3);
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(row));
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(row + 64));
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(row + 128));
-    }
-#endif
     if (g < N) {
         float px = __ldg(means + 3 * g), py = __ldg(means + 3 * g + 1), pz = __ldg(means + 3 * g + 2);
         float4 q = __ldg(reinterpret_cast<const float4*>(quats) + g);

@@ -3,9 +3,6 @@
 #include <stdlib.h>
 #include "raster_common.cuh"
 
-#ifndef RF_VARIANT
-#define RF_VARIANT 1
-#endif
 #ifndef RF_MIN_WARPS
 #define RF_MIN_WARPS 32  // resident warps per SM the register allocation must allow
 #endif
@@ -82,7 +79,10 @@ raster_fwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
             const int idx = stage[j].idx;
 #pragma unroll
             for (int s = 0; s < RU_SLOTS; ++s) {
-#if RF_VARIANT == 2  // branch-free: every slot pays 12 instructions
+                // branch-free slot update (selects, 12 instructions per slot): a pixel the Gaussian does not reach, or
+                // that finishes here, takes w = 0; finishing raises its threshold to +inf.  Measured against a branch
+                // per slot (taken 74 % of the time, 23 of 32 lanes active): 0.2575 -> 0.2495 ms at config A; the
+                // original if/else form (predicated moves + 3 extra MOVs per slot): 0.265 ms.
                 {
                     const float Tn = T[s] * (1.f - al[s]);
                     const bool live = ok[s] && !(Tn <= T_STOP);
@@ -93,20 +93,6 @@ raster_fwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
                     last[s] = live ? idx : last[s];
                     T[s] = live ? Tn : T[s];
                 }
-#else
-                if (ok[s]) {  // a slot no lane reaches is one untaken branch
-                    // selects, not an if/else: ptxas turned the two-way form into predicated moves with three
-                    // extra MOVs per slot; a pixel that finishes here takes w = 0 and raises its threshold to +inf
-                    const float Tn = T[s] * (1.f - al[s]);
-                    const bool live = !(Tn <= T_STOP);
-                    const float w = live ? al[s] * T[s] : 0.f;
-                    thr[s] = live ? thr[s] : INF;
-                    if (HAS_RGB) { acc[s][0] = fmaf(w, col.x, acc[s][0]); acc[s][1] = fmaf(w, col.y, acc[s][1]); acc[s][2] = fmaf(w, col.z, acc[s][2]); }
-                    if (HAS_D) acc[s][CH - 1] = fmaf(w, col.w, acc[s][CH - 1]);
-                    last[s] = live ? idx : last[s];
-                    T[s] = live ? Tn : T[s];
-                }
-#endif
             }
         }
         __syncwarp();

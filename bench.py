@@ -221,6 +221,8 @@ def run_b200(args):
     params_list = [leaves[k] for k in ("means3D", "scales", "rotations", "opacities", "shs")]
     flat = None
 
+    # views of a step alternate over `--view-streams` CUDA streams (streams.py): the short latency-bound kernels and the
+    # drain phase of one view run under the long blend kernels of the other
     vstreams = pkg.ViewStreams(dev, args.view_streams, params_list)
 
     def view_index(step, v):
@@ -262,32 +264,35 @@ def run_b200(args):
         """through the public backend call with HOST buffers: pose + ground-truth frame uploaded from pinned
         memory every view, L1 + D-SSIM loss, backward, loss read back (what trainer.py:270-281,485-497 does per view)."""
         nonlocal flat
-        cur = torch.cuda.current_stream()
         for p in params_list:
             p.grad = None
-        tot = torch.zeros((), device=dev)
+        losses = []
+        vstreams.begin()
         for v in range(V):
-            k = e2e_state["k"]
-            slot = k & 1
-            if not e2e_state["primed"]:
-                for sl in range(2):
-                    free_ev[sl].record(cur)
-                upload(slot, view_index(step, v))
-                e2e_state["primed"] = True
-            nv, ns = (v + 1, step) if v + 1 < V else (0, step + 1)
-            upload(slot ^ 1, view_index(ns, nv))  # prefetch the next view while this one renders
-            cur.wait_event(ready_ev[slot])
-            vp = {"world_view_transform": pose_slot[slot], "image_width": W, "image_height": H}
-            res = backend.render_with_depth(leaves, vp, bg_color=bg, render_mode="RGB", device="cuda", sh_degree=deg)
-            # the reference's per-view loss (trainer.py:485-492: clamp, L1 + 0.2 D-SSIM), value and gradient in one kernel
-            loss = pkg.l1_ssim_loss(res["render"], gt_slot[slot], 0.2)["loss"]
-            loss.backward()
-            free_ev[slot].record(cur)
-            tot = tot + loss.detach()
-            e2e_state["k"] = k + 1
+            with vstreams.view(v):
+                cur = torch.cuda.current_stream()
+                k = e2e_state["k"]
+                slot = k & 1
+                if not e2e_state["primed"]:
+                    for sl in range(2):
+                        free_ev[sl].record(cur)
+                    upload(slot, view_index(step, v))
+                    e2e_state["primed"] = True
+                nv, ns = (v + 1, step) if v + 1 < V else (0, step + 1)
+                upload(slot ^ 1, view_index(ns, nv))  # prefetch the next view while this one renders
+                cur.wait_event(ready_ev[slot])
+                vp = {"world_view_transform": pose_slot[slot], "image_width": W, "image_height": H}
+                res = backend.render_with_depth(leaves, vp, bg_color=bg, render_mode="RGB", device="cuda", sh_degree=deg)
+                # the reference's per-view loss (trainer.py:485-492: clamp, L1 + 0.2 D-SSIM), value and gradient in one kernel
+                loss = pkg.l1_ssim_loss(res["render"], gt_slot[slot], 0.2)["loss"]
+                loss.backward()
+                free_ev[slot].record(cur)
+                losses.append(loss.detach())
+                e2e_state["k"] = k + 1
+        vstreams.join()
         if world > 1:
             flat = pkg.allreduce_gradients(params_list, world * V, flat=flat)
-        return float(tot.item())  # D2H read of the step's result
+        return float(torch.stack(losses).sum().item())  # D2H read of the step's result
 
     # f1 (SURVEY §8f): the same step from the RAW parameter store — activations fused into the kernels, gradients
     # accumulated in-kernel into the flat buffer that the all-reduce then takes as is
@@ -315,32 +320,35 @@ def run_b200(args):
     train_state = {"k": 0, "primed": False}
 
     def step_train(step):
-        cur = torch.cuda.current_stream()
         store.zero_grad()
-        tot = torch.zeros((), device=dev)
+        losses = []
+        vstreams.begin()
         for v in range(V):
-            k = train_state["k"]
-            slot = k & 1
-            if not train_state["primed"]:
-                for sl in range(2):
-                    free_ev[sl].record(cur)
-                upload(slot, view_index(step, v))
-                train_state["primed"] = True
-            nv, ns = (v + 1, step) if v + 1 < V else (0, step + 1)
-            upload(slot ^ 1, view_index(ns, nv))
-            cur.wait_event(ready_ev[slot])
-            vp = {"world_view_transform": pose_slot[slot], "image_width": W, "image_height": H}
-            res = store.render(K, vp, bg_color=bg, render_mode="RGB", sh_degree=deg)
-            loss = pkg.l1_ssim_loss(res["render"], gt_slot[slot], 0.2)["loss"] * (1.0 / V)
-            loss.backward()
-            free_ev[slot].record(cur)
-            tot = tot + loss.detach()
-            train_state["k"] = k + 1
+            with vstreams.view(v):
+                cur = torch.cuda.current_stream()
+                k = train_state["k"]
+                slot = k & 1
+                if not train_state["primed"]:
+                    for sl in range(2):
+                        free_ev[sl].record(cur)
+                    upload(slot, view_index(step, v))
+                    train_state["primed"] = True
+                nv, ns = (v + 1, step) if v + 1 < V else (0, step + 1)
+                upload(slot ^ 1, view_index(ns, nv))
+                cur.wait_event(ready_ev[slot])
+                vp = {"world_view_transform": pose_slot[slot], "image_width": W, "image_height": H}
+                res = store.render(K, vp, bg_color=bg, render_mode="RGB", sh_degree=deg)
+                loss = pkg.l1_ssim_loss(res["render"], gt_slot[slot], 0.2)["loss"] * (1.0 / V)
+                loss.backward()
+                free_ev[slot].record(cur)
+                losses.append(loss.detach())
+                train_state["k"] = k + 1
+        vstreams.join()
         if world > 1:
             pkg.allreduce_flat(store.flat_grad, 1.0 / world)
         adam.step()
         pkg.densify_stats(store.xyz_gradient_accum, store.xyz_gradient_count, store.xyz.grad)
-        return float(tot.item())
+        return float(torch.stack(losses).sum().item())
 
     def timed(fn, steps, warmup, timer=None):
         for i in range(warmup):
@@ -376,6 +384,14 @@ def run_b200(args):
     if rank == 0:
         sampler.start()
     ms_dev, launches = timed(step_device, args.steps, args.warmup, timer)
+    timer_one = None
+    if args.view_streams > 1:  # per-stage durations without the other view's kernels in between (not the headline)
+        multi, vstreams = vstreams, pkg.ViewStreams(dev, 1)
+        timer_one = StageTimer(torch)
+        pkg._lib.stage_timer = timer_one
+        timed(step_device, max(2, args.steps // 4), 1, timer_one)
+        vstreams = multi
+        pkg._lib.stage_timer = timer
     ms_e2e, _ = timed(step_e2e, args.steps, max(1, args.warmup // 2))
     ms_store, _ = timed(step_store, args.steps, max(1, args.warmup // 2))
     ms_train, _ = timed(step_train, args.steps, max(1, args.warmup // 2))
@@ -438,6 +454,12 @@ def run_b200(args):
                     "traffic": traffic, "binding_resource": "FP32/SFU issue slots (not HBM) for raster_fwd / raster_bwd, see "
                     "profiles/ncu_r01_summary.md" if dom.startswith("raster") else "HBM", "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
                     "share_of_step": round(per_view_ms[dom] / sum(per_view_ms.values()), 3), "stages": stages}
+        if timer_one is not None:
+            t1, c1 = timer_one.totals_ms(), timer_one.counts()
+            roofline["stages_note"] = (f"'stages' are CUDA-event brackets inside the timed region, where {args.view_streams} views are in "
+                                       "flight on alternating streams: a bracket also holds whatever the other view ran in between. "
+                                       "'stages_one_stream_ms' is the same step on ONE stream (separate short pass, not the headline).")
+            roofline["stages_one_stream_ms"] = {k: round(t1[k] / max(c1[k], 1), 4) for k in t1}
 
     cpu_baseline = None
     try:
@@ -461,7 +483,7 @@ def run_b200(args):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.config}: {N} gaussians SH{deg}, {W}x{H}, {V} view(s)/rank/step fwd+bwd"
                                + (", gradients all-reduced in place (5 attribute tensors back to back; the store path reduces ONE flat 59N-float buffer) once per step" if world > 1 else ""),
-                   "N": N, "N_visible": n_vis, "M_isects": M, "views_per_rank": V,
+                   "N": N, "N_visible": n_vis, "M_isects": M, "views_per_rank": V, "view_streams": args.view_streams,
                    "l2": "inputs larger than L2 (params 236 MB + keys/records > 126 MB); no explicit flush"},
         "e2e": {"value": e2e_val, "unit": "Mpix/s", "h2d_bytes_per_step": V * (W * H * 3 * 4 + 64), "d2h_bytes_per_step": 4,
                 "ms_per_step": ms_e2e / args.steps},
@@ -497,7 +519,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", default="A", choices=sorted(CONFIGS))
     ap.add_argument("--views-per-rank", type=int, default=4)
-    ap.add_argument("--view-streams", type=int, default=1,
+    ap.add_argument("--view-streams", type=int, default=2,
                     help="CUDA streams the views of a step alternate over (ViewStreams); 1 = one stream")
     ap.add_argument("--total-views", type=int, default=0,
                     help="fixed number of views per step split over the ranks (strong scaling, config B: 64); "
