@@ -151,12 +151,42 @@ struct ShCount {
     static constexpr int NV = (NF + 3) / 4;
 };
 
+#ifndef SH_LDG256
+#define SH_LDG256 1  // 32-byte loads of the SH row where its start is 32-B aligned (sm_100: LDG.E.256)
+#endif
+
+// One 32-byte read-only load (sm_100a).  A lane that walks its own 192-B SH row with 16-byte loads touches every
+// 32-B sector twice and relies on L1 to keep it between the two; with 32-byte loads each sector is one request.
+struct F8 { float v[8]; };
+__device__ __forceinline__ F8 ldg256(const float* p) {
+    F8 r;
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(r.v[0]), "=f"(r.v[1]), "=f"(r.v[2]), "=f"(r.v[3]), "=f"(r.v[4]), "=f"(r.v[5]), "=f"(r.v[6]), "=f"(r.v[7])
+                 : "l"(p));
+    return r;
+}
+
+// vec_ok: 0 = scalar loads, 1 = rows start 16-B aligned, 2 = rows start 32-B aligned
 template <int DEG>
-__device__ __forceinline__ void load_sh(const float* __restrict__ shs, int64_t g, int sh_coeffs, bool vec_ok,
+__device__ __forceinline__ void load_sh(const float* __restrict__ shs, int64_t g, int sh_coeffs, int vec_ok,
                                         float* c /* NV*4 */) {
     constexpr int NV = ShCount<DEG>::NV;
     constexpr int NF = ShCount<DEG>::NF;
     const float* base = shs + g * (int64_t)sh_coeffs * 3;
+#if SH_LDG256
+    if (vec_ok == 2) {
+#pragma unroll
+        for (int i = 0; i < NV / 2; ++i) {
+            const F8 v = ldg256(base + 8 * i);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) c[8 * i + k] = v.v[k];
+        }
+        if (NV & 1) {
+            float4 v = __ldg(reinterpret_cast<const float4*>(base) + (NV - 1));
+            c[4 * NV - 4] = v.x; c[4 * NV - 3] = v.y; c[4 * NV - 2] = v.z; c[4 * NV - 1] = v.w;
+        }
+    } else
+#endif
     if (vec_ok) {
         const float4* b4 = reinterpret_cast<const float4*>(base);
 #pragma unroll
@@ -177,7 +207,7 @@ template <int DEG, bool RAW>
 __global__ void __launch_bounds__(PROJ_THREADS)
 project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__ quats,
                       const float* __restrict__ scales, const float* __restrict__ opacities,
-                      const float* __restrict__ shs, int sh_coeffs, bool vec_ok, int64_t N,
+                      const float* __restrict__ shs, int sh_coeffs, int vec_ok, int64_t N,
                       int32_t* __restrict__ radii, float* __restrict__ splats,
                       int32_t* __restrict__ tiles_per_gauss, int64_t* __restrict__ block_sums,
                       uint32_t* __restrict__ depth_keys, int32_t* __restrict__ gauss_ids,
@@ -323,7 +353,7 @@ template <int DEG, int MODE>
 __global__ void __launch_bounds__(PROJ_THREADS, 2)
 project_sh_bwd_kernel(const float* __restrict__ means, const float* __restrict__ quats,
                       const float* __restrict__ scales, const float* __restrict__ opacities,
-                      const float* __restrict__ shs, int sh_coeffs, bool vec_ok, int64_t N,
+                      const float* __restrict__ shs, int sh_coeffs, int vec_ok, int64_t N,
                       const int32_t* __restrict__ radii, const float* __restrict__ v_splats,
                       float* __restrict__ v_means, float* __restrict__ v_quats, float* __restrict__ v_scales,
                       float* __restrict__ v_opacities, float* __restrict__ v_shs, const Cam* __restrict__ cam_g) {
@@ -615,7 +645,8 @@ static int project_fwd_impl(bool raw, const float* means, const float* quats, co
     B200_REQUIRE((cam_host != nullptr) != (cam_dev != nullptr), "exactly one of cam_host / cam_dev");
     B200_REQUIRE(((uintptr_t)quats & 15) == 0 && ((uintptr_t)splats & 15) == 0 && ((uintptr_t)radii & 7) == 0, "misaligned pointer");
     B200_REQUIRE((depth_keys == nullptr) == (gauss_ids == nullptr), "depth_keys and gauss_ids go together");
-    bool vec_ok = sh_degree >= 0 && ((sh_coeffs * 12) % 16 == 0) && (((uintptr_t)shs & 15) == 0);
+    int vec_ok = sh_degree >= 0 && ((sh_coeffs * 12) % 16 == 0) && (((uintptr_t)shs & 15) == 0);
+    if (vec_ok && ((sh_coeffs * 12) % 32 == 0) && (((uintptr_t)shs & 31) == 0)) vec_ok = 2;
     dim3 grid((unsigned)b200_project_blocks(N)), block(PROJ_THREADS);
     cudaStream_t st = (cudaStream_t)stream;
     int cdev = -1;
@@ -664,7 +695,8 @@ static int project_bwd_impl(int mode, const float* means, const float* quats, co
     B200_REQUIRE((cam_host != nullptr) != (cam_dev != nullptr), "exactly one of cam_host / cam_dev");
     B200_REQUIRE(means && quats && scales && opacities && shs && radii && v_splats && v_means && v_quats && v_scales && v_opacities && v_shs, "null pointer");
     B200_REQUIRE(((uintptr_t)quats & 15) == 0 && ((uintptr_t)v_splats & 15) == 0 && ((uintptr_t)v_quats & 15) == 0 && ((uintptr_t)radii & 7) == 0, "misaligned pointer");
-    bool vec_ok = sh_degree >= 0 && ((sh_coeffs * 12) % 16 == 0) && (((uintptr_t)shs & 15) == 0) && (((uintptr_t)v_shs & 15) == 0);
+    int vec_ok = sh_degree >= 0 && ((sh_coeffs * 12) % 16 == 0) && (((uintptr_t)shs & 15) == 0) && (((uintptr_t)v_shs & 15) == 0);
+    if (vec_ok && ((sh_coeffs * 12) % 32 == 0) && (((uintptr_t)shs & 31) == 0)) vec_ok = 2;
     dim3 grid((unsigned)b200_project_blocks(N)), block(PROJ_THREADS);
     cudaStream_t st = (cudaStream_t)stream;
     int cdev = -1;
