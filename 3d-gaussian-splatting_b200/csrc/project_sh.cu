@@ -200,10 +200,50 @@ __device__ __forceinline__ void load_sh(const float* __restrict__ shs, int64_t g
     }
 }
 
+// ---- bulk-async (TMA engine) staging of SH rows -------------------------------------------------------------------
+// A lane that fetches its own 192-B SH row with vector loads sends six to twelve single-sector requests down the
+// LSU -> L1 -> L2 path, next to the kernel's other scattered traffic (record stores, the four tile-grid REDs).  In BULK
+// mode every visible lane instead issues ONE cp.async.bulk (SASS UBLKCP) of its row into a padded shared-memory row:
+// the copy engine moves whole rows, completion is signalled on one mbarrier per warp (expect_tx = rows x bytes), and
+// the lane then reads its row with conflict-free LDS.128 (row stride 13 x 16 B: 13 l mod 8 is a permutation of the
+// quarter warp).  Culled Gaussians never touch their SH row, as before.
+#ifndef SH_BULK
+#define SH_BULK 1
+#endif
+#ifndef SH_BULK_EARLY
+#define SH_BULK_EARLY 0
+#endif
+#define SH_ROW_F 52  // padded shared-memory row stride in floats (48 used at degree 3)
+#define SH_BULK_SMEM (PROJ_THREADS * SH_ROW_F * 4 + (PROJ_THREADS / 32) * 8)
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
 // RAW: the inputs are the reference's raw parameters (gaussian_model.py:65-76) and the getters' activations
 // (gaussian_model.py:90-108: exp / sigmoid; F.normalize is the quaternion normalisation done here anyway) are
 // applied in registers — no activated copies of the parameter store are ever materialised.
-template <int DEG, bool RAW>
+// BULK: SH rows staged by cp.async.bulk (above); needs 16-B aligned rows and SH_BULK_SMEM bytes of dynamic shared memory.
+template <int DEG, bool RAW, bool BULK>
 __global__ void __launch_bounds__(PROJ_THREADS)
 project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__ quats,
                       const float* __restrict__ scales, const float* __restrict__ opacities,
@@ -212,21 +252,47 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
                       int32_t* __restrict__ tiles_per_gauss, int64_t* __restrict__ block_sums,
                       uint32_t* __restrict__ depth_keys, int32_t* __restrict__ gauss_ids,
                       int32_t* __restrict__ tile_grid, const Cam* __restrict__ cam_g) {
-    STAGE_CAM(cam_g);
+    extern __shared__ __align__(128) unsigned char s_dyn[];
+    float* s_sh = reinterpret_cast<float*>(s_dyn);
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_dyn + PROJ_THREADS * SH_ROW_F * 4) + (threadIdx.x >> 5);
+    if (BULK) {
+        if ((threadIdx.x & 31) == 0) mbar_init(s_bar, 1);
+    }
+    STAGE_CAM(cam_g);  // (block barrier: orders the mbarrier initialisation as well)
     int64_t g = (int64_t)blockIdx.x * PROJ_THREADS + threadIdx.x;
+    if (BULK && SH_BULK_EARLY) {  // probe: fetch every row before the cull decision
+        constexpr int D = DEG < 0 ? 0 : DEG;
+        constexpr uint32_t ROW_BYTES = ShCount<D>::NV * 16;
+        const unsigned vmask = __ballot_sync(0xffffffffu, g < N);
+        if ((threadIdx.x & 31) == 0) mbar_arrive_expect_tx(s_bar, ROW_BYTES * (uint32_t)__popc(vmask));
+        if (g < N) bulk_g2s(s_sh + threadIdx.x * SH_ROW_F, shs + g * (int64_t)sh_coeffs * 3, ROW_BYTES, s_bar);
+    }
     int ntiles = 0;
+    float px = 0.f, py = 0.f, pz = 0.f, opac = 0.f;
+    Proj P;
+    int rx = 0, ry = 0;
+    bool ok = false;
     if (g < N) {
-        float px = __ldg(means + 3 * g), py = __ldg(means + 3 * g + 1), pz = __ldg(means + 3 * g + 2);
+        px = __ldg(means + 3 * g); py = __ldg(means + 3 * g + 1); pz = __ldg(means + 3 * g + 2);
         float4 q = __ldg(reinterpret_cast<const float4*>(quats) + g);
         float sx = __ldg(scales + 3 * g), sy = __ldg(scales + 3 * g + 1), sz = __ldg(scales + 3 * g + 2);
-        float opac = __ldg(opacities + g);
+        opac = __ldg(opacities + g);
         if (RAW) {
             sx = expf(sx); sy = expf(sy); sz = expf(sz);
             opac = 1.f / (1.f + expf(-opac));
         }
-        Proj P;
-        int rx = 0, ry = 0;
-        bool ok = project_core(cam, px, py, pz, q, sx, sy, sz, P) && radius_and_cull(cam, P, opac, rx, ry);
+        ok = project_core(cam, px, py, pz, q, sx, sy, sz, P) && radius_and_cull(cam, P, opac, rx, ry);
+    }
+    if (BULK && !SH_BULK_EARLY) {  // every lane of the warp gets here
+        constexpr int D = DEG < 0 ? 0 : DEG;
+        constexpr uint32_t ROW_BYTES = ShCount<D>::NV * 16;
+        const unsigned vmask = __ballot_sync(0xffffffffu, ok);
+        if (vmask != 0u) {
+            if ((threadIdx.x & 31) == 0) mbar_arrive_expect_tx(s_bar, ROW_BYTES * (uint32_t)__popc(vmask));
+            if (ok) bulk_g2s(s_sh + threadIdx.x * SH_ROW_F, shs + g * (int64_t)sh_coeffs * 3, ROW_BYTES, s_bar);
+        }
+    }
+    if (g < N) {
         float4 r0 = make_float4(0.f, 0.f, 0.f, 0.f), r1 = r0, r2 = r0;
         if (ok) {
             float col[3];
@@ -234,11 +300,21 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
                 constexpr int D = DEG < 0 ? 0 : DEG;
                 constexpr int NB = ShCount<D>::NB;
                 float c[ShCount<D>::NV * 4];
-                load_sh<D>(shs, g, sh_coeffs, vec_ok, c);
                 float ux = px - cam.campos[0], uy = py - cam.campos[1], uz = pz - cam.campos[2];
                 float inv = rsqrtf(ux * ux + uy * uy + uz * uz);
                 float B[NB];
                 sh_basis<D>(ux * inv, uy * inv, uz * inv, B);
+                if (BULK) {
+                    mbar_wait(s_bar, 0);
+                    const float4* row = reinterpret_cast<const float4*>(s_sh + threadIdx.x * SH_ROW_F);
+#pragma unroll
+                    for (int i = 0; i < ShCount<D>::NV; ++i) {
+                        const float4 v = row[i];
+                        c[4 * i + 0] = v.x; c[4 * i + 1] = v.y; c[4 * i + 2] = v.z; c[4 * i + 3] = v.w;
+                    }
+                } else {
+                    load_sh<D>(shs, g, sh_coeffs, vec_ok, c);
+                }
                 float r = 0.f, gg = 0.f, b = 0.f;
 #pragma unroll
                 for (int k = 0; k < NB; ++k) {
@@ -652,8 +728,16 @@ static int project_fwd_impl(bool raw, const float* means, const float* quats, co
     int cdev = -1;
     const Cam* cam_g = load_cam(cam_host, cam_dev, width, height, st, &cdev);
     if (cam_g == nullptr) return B200_ECUDA;
-#define LAUNCH(D) do { if (raw) project_sh_fwd_kernel<D, true><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, cam_g); \
-                       else project_sh_fwd_kernel<D, false><<<grid, block, 0, st>>>(means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, cam_g); } while (0)
+    // BULK staging of the SH rows needs 16-B aligned rows; the dynamic shared-memory limit is raised once per instantiation
+    const bool bulk = SH_BULK && sh_degree >= 0 && vec_ok != 0;
+#define FWD_ARGS means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, cam_g
+#define LAUNCH_B(D, R) do { \
+        static bool attr_set = false; \
+        if (!attr_set) { cudaFuncSetAttribute(project_sh_fwd_kernel<D, R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SH_BULK_SMEM); attr_set = true; } \
+        project_sh_fwd_kernel<D, R, true><<<grid, block, SH_BULK_SMEM, st>>>(FWD_ARGS); } while (0)
+#define LAUNCH(D) do { if (bulk && D >= 0) { if (raw) LAUNCH_B((D < 0 ? 0 : D), true); else LAUNCH_B((D < 0 ? 0 : D), false); } \
+                       else if (raw) project_sh_fwd_kernel<D, true, false><<<grid, block, 0, st>>>(FWD_ARGS); \
+                       else project_sh_fwd_kernel<D, false, false><<<grid, block, 0, st>>>(FWD_ARGS); } while (0)
     switch (sh_degree) {
         case 0: LAUNCH(0); break;
         case 1: LAUNCH(1); break;
@@ -662,6 +746,8 @@ static int project_fwd_impl(bool raw, const float* means, const float* quats, co
         default: LAUNCH(-1); break;
     }
 #undef LAUNCH
+#undef LAUNCH_B
+#undef FWD_ARGS
     cam_used(cdev, st);
     return b200_check_launch("project_sh_fwd");
 }
