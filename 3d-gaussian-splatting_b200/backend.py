@@ -62,8 +62,8 @@ class B200Backend:
             render_mode="RGB+ED", sh_degree=sh_degree,
             backgrounds=bg_color[None, ...] if bg_color.dim() == 1 else bg_color,
         )
-        rendered = renders[0]
-        result = {"render": rendered[..., :3], "alpha": alphas[0], "depth": rendered[..., 3]}
+        rendered = renders.squeeze(0)  # one camera: squeeze is a view both ways (select's backward = zeros + full-image copy)
+        result = {"render": rendered[..., :3], "alpha": alphas.squeeze(0), "depth": rendered[..., 3]}
         result["means2d"] = meta["means2d"][0]
         result["radii"] = meta["radii"][0]
         result["visibility_filter"] = result["radii"] > 0
@@ -93,8 +93,8 @@ class B200Backend:
             width=viewpoint["image_width"], height=viewpoint["image_height"], packed=False,
             render_mode=render_mode, sh_degree=sh_degree, backgrounds=bg_color[None, ...],
         )
-        output = renders[0]
-        alpha = alphas[0]
+        output = renders.squeeze(0)  # one camera: squeeze is a view both ways (select's backward = zeros + full-image copy)
+        alpha = alphas.squeeze(0)
         result = {"alpha": alpha}
         if render_mode == "RGB":
             result["render"] = output

@@ -189,7 +189,7 @@ class GaussianStore(nn.Module):
             sh_degree=sh_degree, render_mode=render_mode,
             backgrounds=None if bg_color is None else bg_color[None], raw_params=True,
             grad_into=self.grad_buffers() if (accumulate_grads and torch.is_grad_enabled()) else None)
-        out, alpha = renders[0], alphas[0]
+        out, alpha = renders.squeeze(0), alphas.squeeze(0)  # views both ways (select's backward = zeros + full-image copy)
         result = {"alpha": alpha, "means2d": meta["means2d"][0], "radii": meta["radii"][0]}
         result["visibility_filter"] = result["radii"] > 0
         if render_mode == "RGB":

@@ -52,3 +52,8 @@ for a, b in zip(ev, ev[1:]):
     s = gaps.setdefault(k, [0, 0.0]); s[0] += 1; s[1] += max(g, 0)
 for k, (n, g) in sorted(gaps.items(), key=lambda x: -x[1][1])[:8]:
     print(f"{g/n:8.1f} us x{n:3d}  after {k[0]:40s} before {k[1]}")
+if os.environ.get("SEQ"):  # launch order of the first ~2 views with start offsets, durations and the gap in front
+    prev = ev[0].time_range.start
+    for e in ev[:int(os.environ["SEQ"])]:
+        print(f"  +{(e.time_range.start - t0)/1e3:8.3f} ms  gap {max(e.time_range.start - prev, 0):7.1f} us  dur {e.time_range.end - e.time_range.start:7.1f} us  {e.name[:70]}")
+        prev = e.time_range.end
