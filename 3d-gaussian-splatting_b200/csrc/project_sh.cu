@@ -361,7 +361,9 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
             gauss_ids[g] = (int32_t)g;
         }
     }
-    // block sum of tile counts (feeds b200_bin_scan)
+    // block sum of tile counts (feeds b200_bin_scan on the 64-bit-key path; the split-key path recounts in depth order
+    // and passes no buffer, which spares the CTA its closing barrier)
+    if (block_sums == nullptr) return;
     __shared__ int warp_tot[PROJ_THREADS / 32];
     int v = ntiles;
 #pragma unroll
@@ -717,7 +719,8 @@ static int project_fwd_impl(bool raw, const float* means, const float* quats, co
         cudaMemsetAsync(tile_grid, 0, cells * sizeof(int32_t), (cudaStream_t)stream);
     }
     if (N == 0) return B200_OK;
-    B200_REQUIRE(means && quats && scales && opacities && shs && radii && splats && tiles_per_gauss && block_sums, "null pointer");
+    B200_REQUIRE(means && quats && scales && opacities && shs && radii && splats && tiles_per_gauss, "null pointer");
+    B200_REQUIRE(block_sums != nullptr || depth_keys != nullptr, "block_sums may be omitted only on the split-key path (depth_keys given)");
     B200_REQUIRE((cam_host != nullptr) != (cam_dev != nullptr), "exactly one of cam_host / cam_dev");
     B200_REQUIRE(((uintptr_t)quats & 15) == 0 && ((uintptr_t)splats & 15) == 0 && ((uintptr_t)radii & 7) == 0, "misaligned pointer");
     B200_REQUIRE((depth_keys == nullptr) == (gauss_ids == nullptr), "depth_keys and gauss_ids go together");

@@ -146,7 +146,7 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
     with _stage("project_sh_fwd"):
         check(project_fwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors),
                                       sh_coeffs, deg, N, None, _ptr(cam), width, height, _ptr(radii), _ptr(splats),
-                                      _ptr(tiles_per_gauss), _ptr(block_sums),
+                                      _ptr(tiles_per_gauss), None if split else _ptr(block_sums),  # split: recounted in depth order
                                       _ptr(dkeys_a) if split else None, _ptr(gids_a) if split else None,
                                       _ptr(tile_grid), st),
               "b200_project_sh_fwd", kernels=1 if N > 0 else 0)

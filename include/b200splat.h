@@ -73,7 +73,8 @@ int b200_cam_pack(const float* viewmat, const float* K, float near_plane, float 
  *   means[N,3] quats[N,4] scales[N,3] (post-exp) opacities[N] (post-sigmoid) shs[N,sh_coeffs,3]
  *   sh_degree in 0..3 with (sh_degree+1)^2 <= sh_coeffs; sh_degree < 0 => `shs` is [N,3] plain colours.
  * Outputs: radii[N,2] int32, splats[N,12], tiles_per_gauss[N] int32,
- *          block_sums[b200_project_blocks(N)] int64 (sum of tiles_per_gauss per 256-Gaussian block);
+ *          block_sums[b200_project_blocks(N)] int64 (sum of tiles_per_gauss per 256-Gaussian block; may be NULL
+ *          when depth_keys is given — the split-key path recounts in depth order, b200_bin_count_sorted);
  *          optional (both or neither NULL) depth_keys[N] uint32 = fp32 depth bits (0xFFFFFFFF if culled)
  *          and gauss_ids[N] = 0..N-1, the input of the split-key sort below.
  *          optional tile_grid[(tile_h+1)*(tile_w+1)] int32 (zeroed by this call): +1/-1 at the corners of

@@ -94,6 +94,34 @@ def test_culling_cases(pkg, oracle):
     assert torch.equal(radii, proj["radii"])
 
 
+@pytest.mark.parametrize("deg", [0, 1, 2, 3])
+@pytest.mark.parametrize("shift", [1, 4])
+def test_sh_row_fetch_paths_agree(pkg, oracle, deg, shift):
+    """The SH rows reach the projection kernels three ways: cp.async.bulk staging (forward) / 32-byte loads (backward)
+    when the rows are 16- / 32-byte aligned, 16-byte loads, and scalar loads when they are not (a view that starts
+    `shift` floats into a larger allocation).  Colours, render and SH gradients must not depend on which one ran."""
+    N, W, H = 5000, 160, 96
+    sc, act = _scene(oracle, N, W, H, seed=3)
+    a = _cuda(act)
+    vm, K = sc["viewmat"].to(DEV)[None], sc["K"].to(DEV)[None]
+    v = torch.randn(1, H, W, 3, generator=torch.Generator().manual_seed(5)).to(DEV)
+    out = []
+    for sft in (0, shift):
+        buf = torch.zeros(N * 48 + 8, device=DEV)
+        shs = buf[sft:sft + N * 48].view(N, 16, 3)
+        shs.copy_(a["shs"])
+        shs.requires_grad_(True)
+        assert (shs.data_ptr() % 16 == 0) == (sft % 4 == 0)
+        r, _, meta = pkg.rasterization(a["means3D"], a["rotations"], a["scales"], a["opacities"].view(-1), shs, vm, K, W, H,
+                                       sh_degree=deg)
+        r.backward(v)
+        out.append((r.detach().clone(), meta["colors"].clone(), shs.grad.clone()))
+    (r0, c0, g0), (r1, c1, g1) = out
+    assert torch.equal(r0, r1) and torch.equal(c0, c1)
+    # the cotangents reach the SH VJP through float atomics (order varies run to run), so the gradients are compared to rounding
+    assert torch.allclose(g0, g1, rtol=1e-4, atol=1e-6)
+
+
 # ------------------------------------------------------------------------------------------------
 # stage 2: binning / sort / ranges — bit exact
 # ------------------------------------------------------------------------------------------------
