@@ -200,7 +200,7 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
 
     pkg = importlib.import_module("3d-gaussian-splatting_b200")
-    from oracle import torch_oracle as orc  # scene generator only (deterministic CPU generator)
+    orc = importlib.import_module("3d-gaussian-splatting_b200.synthetic")  # workload generator; oracle/ is not imported on this arm
 
     N, W, H, deg = CONFIGS[args.config]
     V = args.views_per_rank

@@ -198,3 +198,29 @@ def test_oracles_reproduce_the_committed_golden_fixture():
     for k, gref in gold["grads"].items():
         rel = ((grads[k].reshape(gref.shape) - gref).norm() / gref.norm()).item()
         assert rel <= 2e-3, f"{k}: {rel}"
+
+
+# ---- the bench's workload generator (package) and the oracle's copy must produce the same bits -----------
+def test_package_workload_generator_equals_the_oracles():
+    import importlib
+    syn = importlib.import_module("3d-gaussian-splatting_b200.synthetic")
+    a, b = syn.synthetic_scene(3000, 320, 200, seed=4), orc.synthetic_scene(3000, 320, 200, seed=4)
+    assert a.keys() == b.keys() and all(torch.equal(a[k], b[k]) for k in a)
+    aa, bb = syn.activate(a), orc.activate(b)
+    assert all(torch.equal(aa[k], bb[k]) for k in aa)
+    assert torch.equal(syn.circle_cameras(64), orc.circle_cameras(64))
+
+
+def test_product_package_and_b200_bench_arm_never_import_the_oracle():
+    """oracle/ is test infrastructure: the package must not reference it, and bench.py may only do so on the CPU legs."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    pkg_dir = os.path.join(root, "3d-gaussian-splatting_b200")
+    for fn in os.listdir(pkg_dir):
+        if fn.endswith(".py"):
+            src = open(os.path.join(pkg_dir, fn)).read()
+            assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), fn
+    bench_src = open(os.path.join(root, "bench.py")).read()
+    arm = bench_src[bench_src.index("def run_b200("):bench_src.index("def main(")]
+    imports = re.findall(r"^\s*(?:from|import)\s+oracle\b.*$", arm, re.M)
+    assert imports == [], imports  # cpu_baseline goes through cpu_port_time(), defined outside the arm
