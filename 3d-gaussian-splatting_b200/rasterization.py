@@ -134,7 +134,7 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
     nblocks = int(lib.b200_project_blocks(N))
     block_sums = torch.empty(max(nblocks, 1), dtype=torch.int64, device=dev)
     block_offsets = torch.empty(max(nblocks, 1), dtype=torch.int64, device=dev)
-    total = torch.zeros(1, dtype=torch.int64, device=dev)
+    total = torch.empty(1, dtype=torch.int64, device=dev)  # written (not accumulated) by b200_bin_scan
     split = method in ("split", "split-hist")
     # tile ranges + radix digit bases from the corner-difference grid (b200_tile_prep) when the grid fits
     prep = method == "split" and (tile_w + 1) * (tile_h + 1) <= int(lib.b200_tile_prep_max_cells())
