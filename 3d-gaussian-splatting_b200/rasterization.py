@@ -314,7 +314,15 @@ class RasterizeSplats(torch.autograd.Function):
                 sh_coeffs, deg = 1, -1
             else:
                 sh_coeffs, deg = colors.shape[1], int(sh_degree)
+            write_first = False
             if grad_into is not None:
+                # optional sixth element: the store's lazy-zero state — the first backward after zero_grad(lazy=True)
+                # writes the buffers (as the non-accumulating mode does), the following ones add to them
+                state = grad_into[5] if len(grad_into) > 5 else None
+                grad_into = tuple(grad_into[:5])
+                if state is not None and state.get("pending_zero"):
+                    write_first = True
+                    state["pending_zero"] = False
                 v_means, v_quats, v_scales, v_opac, v_colors = grad_into
                 for gbuf, ref in zip(grad_into, (means, quats, scales, opacities, colors)):
                     if gbuf.numel() != ref.numel() or not gbuf.is_contiguous() or gbuf.dtype != torch.float32:
@@ -339,7 +347,8 @@ class RasterizeSplats(torch.autograd.Function):
                                                       _ptr(colors), sh_coeffs, deg, N, None, _ptr(cam), width, height,
                                                       _ptr(radii), _ptr(v_splats), _ptr(v_means), _ptr(v_quats),
                                                       _ptr(v_scales), _ptr(v_opac), _ptr(v_colors),
-                                                      1 if grad_into is not None else 0, st), "b200_project_sh_bwd_raw")
+                                                      1 if (grad_into is not None and not write_first) else 0, st),
+                          "b200_project_sh_bwd_raw")
                 else:
                     check(lib.b200_project_sh_bwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors),
                                                   sh_coeffs, deg, N, None, _ptr(cam), width, height, _ptr(radii),

@@ -63,14 +63,17 @@ class GaussianStore(nn.Module):
             o += _align4(n * w)
         self._offsets, self._n = offs, n
         self.flat = torch.zeros(o, dtype=torch.float32, device=dev)
-        self.flat_grad = torch.zeros(o, dtype=torch.float32, device=dev)
+        self._flat_grad = torch.zeros(o, dtype=torch.float32, device=dev)
+        # shared with the backward pass (rasterization.RasterizeSplats): True after zero_grad(lazy=True) until the first
+        # backward has WRITTEN the buffer instead of adding into it
+        self._grad_state = {"pending_zero": False}
 
         def view(buf, name, *shape):
             w = dict(_BLOCKS)[name]
             return buf[offs[name]: offs[name] + n * w].view(n, *shape)
 
         feats = view(self.flat, "features", 16, 3)
-        gfeats = view(self.flat_grad, "features", 16, 3)
+        gfeats = view(self._flat_grad, "features", 16, 3)
         self.xyz = nn.Parameter(view(self.flat, "xyz", 3))
         self.scaling = nn.Parameter(view(self.flat, "scaling", 3))
         self.rotation = nn.Parameter(view(self.flat, "rotation", 4))
@@ -81,10 +84,10 @@ class GaussianStore(nn.Module):
         # so parameters() lists every float once.
         object.__setattr__(self, "features_dc", nn.Parameter(feats[:, 0:1, :]))
         object.__setattr__(self, "features_rest", nn.Parameter(feats[:, 1:, :]))
-        self.xyz.grad = view(self.flat_grad, "xyz", 3)
-        self.scaling.grad = view(self.flat_grad, "scaling", 3)
-        self.rotation.grad = view(self.flat_grad, "rotation", 4)
-        self.opacity.grad = view(self.flat_grad, "opacity", 1)
+        self.xyz.grad = view(self._flat_grad, "xyz", 3)
+        self.scaling.grad = view(self._flat_grad, "scaling", 3)
+        self.rotation.grad = view(self._flat_grad, "rotation", 4)
+        self.opacity.grad = view(self._flat_grad, "opacity", 1)
         self.features.grad = gfeats
         self.features_dc.grad = gfeats[:, 0:1, :]
         self.features_rest.grad = gfeats[:, 1:, :]
@@ -137,7 +140,7 @@ class GaussianStore(nn.Module):
     def _grad_view(self, name: str) -> torch.Tensor:
         w = dict(_BLOCKS)[name]
         o = self._offsets[name]
-        return self.flat_grad[o: o + self._n * w].view(self._n, *self._SHAPES[name])
+        return self._flat_grad[o: o + self._n * w].view(self._n, *self._SHAPES[name])
 
     def _attach_grads(self) -> bool:
         """Make every ``param.grad`` the matching view of ``flat_grad``; True if any had been detached."""
@@ -161,19 +164,39 @@ class GaussianStore(nn.Module):
         return [{"params": [getattr(self, k)], "lr": lrs[k], "name": k}
                 for k in ("xyz", "features_dc", "features_rest", "scaling", "rotation", "opacity")]
 
-    def zero_grad(self, set_to_none: bool = False) -> None:
+    @property
+    def flat_grad(self) -> torch.Tensor:
+        """The flat gradient buffer (what the all-reduce and the optimiser take).  Reading it after ``zero_grad(lazy=True)``
+        with no backward in between performs the postponed memset, so a reader never sees stale values."""
+        if self._grad_state["pending_zero"]:
+            self._flat_grad.zero_()
+            self._grad_state["pending_zero"] = False
+        return self._flat_grad
+
+    def zero_grad(self, set_to_none: bool = False, lazy: bool = False) -> None:
         """One memset of the flat gradient buffer; the ``.grad`` views stay attached (``set_to_none`` is ignored:
-        the kernels accumulate into the buffer, not into tensors autograd hands out)."""
-        self.flat_grad.zero_()
+        the kernels accumulate into the buffer, not into tensors autograd hands out).
+
+        lazy=True postpones the memset: the first backward of a ``render(accumulate_grads=True)`` that runs afterwards
+        WRITES the buffer (zeros for culled Gaussians and inactive SH coefficients included) and the following ones add
+        to it — no 236 B/Gaussian fill and no read half of the first view's read-modify-write.  Until then the
+        ``param.grad`` views hold the previous step's values; ``flat_grad`` (property) materialises the zeros on demand."""
         self._attach_grads()
+        if lazy:
+            self._grad_state["pending_zero"] = True
+            return
+        self._flat_grad.zero_()
+        self._grad_state["pending_zero"] = False
 
     def grad_buffers(self):
-        """(g_xyz, g_rotation, g_scaling, g_opacity, g_features) in the kernels' argument order."""
+        """(g_xyz, g_rotation, g_scaling, g_opacity, g_features, state) — the kernels' argument order, then the
+        lazy-zero state the backward consults (see ``zero_grad``)."""
         if self._attach_grads():
             # an optimiser's zero_grad(set_to_none=True) dropped the views: honour it as "gradients are zero"
-            self.flat_grad.zero_()
+            self._flat_grad.zero_()
+            self._grad_state["pending_zero"] = False
         return (self._grad_view("xyz"), self._grad_view("rotation"), self._grad_view("scaling"),
-                self._grad_view("opacity").view(-1), self._grad_view("features"))
+                self._grad_view("opacity").view(-1), self._grad_view("features"), self._grad_state)
 
     # ------------------------------------------------------------------ rendering
     def render(self, K: torch.Tensor, viewpoint: Dict, bg_color: Optional[torch.Tensor] = None,

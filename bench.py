@@ -300,7 +300,7 @@ def run_b200(args):
                                            sc["scaling"].to(dev), sc["rotation"].to(dev), sc["opacity"].to(dev))
 
     def step_store(step):
-        store.zero_grad()
+        store.zero_grad(lazy=True)  # the first backward writes the flat gradient buffer (no memset, no read-modify-write)
         vstreams.begin()
         for v in range(V):
             with vstreams.view(v):
@@ -320,7 +320,7 @@ def run_b200(args):
     train_state = {"k": 0, "primed": False}
 
     def step_train(step):
-        store.zero_grad()
+        store.zero_grad(lazy=True)  # the first backward writes the flat gradient buffer (no memset, no read-modify-write)
         losses = []
         vstreams.begin()
         for v in range(V):

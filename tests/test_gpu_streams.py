@@ -82,3 +82,48 @@ def test_store_two_streams_same_gradients(pkg, oracle):
     vs = pkg.ViewStreams(DEV, 2)
     for rep in range(4):
         assert _close(step(vs), g1), rep
+
+
+@pytest.mark.parametrize("deg", [1, 3])
+def test_store_lazy_zero_grad_equals_eager(pkg, oracle, deg):
+    """zero_grad(lazy=True): the first backward writes the flat gradient buffer, the following ones add to it — same
+    gradients as memset + accumulate (one and two view streams, forwards-then-one-backward order included), stale values
+    from the previous step never leak, and reading flat_grad with no backward in between yields zeros."""
+    N, W, H, V = 40000, 320, 200, 4
+    sc = oracle.synthetic_scene(N, W, H, seed=9)
+    st = pkg.GaussianStore.from_tensors(sc["xyz"].to(DEV), sc["features_dc"].to(DEV), sc["features_rest"].to(DEV),
+                                        sc["scaling"].to(DEV), sc["rotation"].to(DEV), sc["opacity"].to(DEV))
+    K = sc["K"].to(DEV)
+    bg = torch.zeros(3, device=DEV)
+    v = torch.randn(H, W, 3, generator=torch.Generator().manual_seed(10)).to(DEV)
+    views = _views(oracle, sc, W, H, V)
+
+    def step(vs, lazy, summed=False):
+        st.zero_grad(lazy=lazy)
+        vs.begin()
+        outs = []
+        for i, vp in enumerate(views):
+            with vs.view(i):
+                r = st.render(K, vp, bg_color=bg, render_mode="RGB", sh_degree=deg)["render"]
+                if summed:
+                    outs.append((r * v).sum())
+                else:
+                    r.backward(v)
+        vs.join()
+        if summed:  # the reference's order: every view rendered, then ONE backward (autograd runs the views in reverse)
+            torch.stack(outs).sum().backward()
+        torch.cuda.synchronize()
+        return st.flat_grad.clone()
+
+    one, two = pkg.ViewStreams(DEV, 1), pkg.ViewStreams(DEV, 2)
+    ref = step(one, lazy=False)
+    assert ref.abs().max().item() > 0
+    st._flat_grad.fill_(123.0)  # poison: a lazy step must overwrite every element the eager one zeroes
+    assert _close(step(one, lazy=True), ref)
+    st._flat_grad.fill_(-7.0)
+    assert _close(step(two, lazy=True), ref)
+    st._flat_grad.fill_(3.0)
+    assert _close(step(one, lazy=True, summed=True), ref)
+    st._flat_grad.fill_(5.0)
+    st.zero_grad(lazy=True)
+    assert st.flat_grad.abs().max().item() == 0.0  # no backward ran: the property performs the postponed memset
