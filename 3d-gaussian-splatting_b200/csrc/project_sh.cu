@@ -293,7 +293,44 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
         }
     }
     if (g < N) {
+        // Everything that depends only on the projection goes out BEFORE the wait on the SH row — the tile-grid REDs, the
+        // small per-Gaussian outputs and the first record vector travel while the copy engine fetches the row instead
+        // of queueing behind it.
         float4 r0 = make_float4(0.f, 0.f, 0.f, 0.f), r1 = r0, r2 = r0;
+        float inv_det = 0.f;
+        if (ok) {
+            // tile rectangle (SURVEY.md A.3) — same fp32 operations as the oracle's tile_bounds
+            float tile_x = P.mx / (float)TILE, tile_y = P.my / (float)TILE;
+            float trx = (float)rx / (float)TILE, try_ = (float)ry / (float)TILE;
+            float fw = (float)cam.tile_w, fh = (float)cam.tile_h;
+            int minx = (int)fminf(fmaxf(floorf(tile_x - trx), 0.f), fw);
+            int maxx = (int)fminf(fmaxf(ceilf(tile_x + trx), 0.f), fw);
+            int miny = (int)fminf(fmaxf(floorf(tile_y - try_), 0.f), fh);
+            int maxy = (int)fminf(fmaxf(ceilf(tile_y + try_), 0.f), fh);
+            ntiles = (maxy - miny) * (maxx - minx);
+            if (tile_grid != nullptr && ntiles > 0) {
+                // corner differences of the tile rectangle: a 2-D prefix sum (b200_tile_prep) turns the grid
+                // into per-tile intersection counts, i.e. the tile ranges and the radix digit histograms,
+                // without another pass over the M intersections
+                const int gs = cam.tile_w + 1;
+                atomicAdd(tile_grid + miny * gs + minx, 1);
+                atomicAdd(tile_grid + miny * gs + maxx, -1);
+                atomicAdd(tile_grid + maxy * gs + minx, -1);
+                atomicAdd(tile_grid + maxy * gs + maxx, 1);
+            }
+            inv_det = 1.f / P.det;
+            r0 = make_float4(P.mx, P.my, P.c * inv_det, -P.b * inv_det);
+        } else {
+            rx = ry = 0;
+        }
+        reinterpret_cast<int2*>(radii)[g] = make_int2(rx, ry);
+        float4* rec = reinterpret_cast<float4*>(splats) + 3 * g;
+        rec[0] = r0;
+        tiles_per_gauss[g] = ntiles;
+        if (depth_keys != nullptr) {  // split-key sort: depth digits are sorted over Gaussians, before duplication
+            depth_keys[g] = ntiles > 0 ? __float_as_uint(P.pcz) : 0xFFFFFFFFu;
+            gauss_ids[g] = (int32_t)g;
+        }
         if (ok) {
             float col[3];
             if (DEG >= 0) {
@@ -326,40 +363,10 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
             } else {  // plain colours [N,3]
                 col[0] = __ldg(shs + 3 * g); col[1] = __ldg(shs + 3 * g + 1); col[2] = __ldg(shs + 3 * g + 2);
             }
-            float inv_det = 1.f / P.det;
-            r0 = make_float4(P.mx, P.my, P.c * inv_det, -P.b * inv_det);
             r1 = make_float4(P.a * inv_det, opac, col[0], col[1]);
             r2 = make_float4(col[2], P.pcz, 0.f, 0.f);
-            // tile rectangle (SURVEY.md A.3) — same fp32 operations as the oracle's tile_bounds
-            float tile_x = P.mx / (float)TILE, tile_y = P.my / (float)TILE;
-            float trx = (float)rx / (float)TILE, try_ = (float)ry / (float)TILE;
-            float fw = (float)cam.tile_w, fh = (float)cam.tile_h;
-            int minx = (int)fminf(fmaxf(floorf(tile_x - trx), 0.f), fw);
-            int maxx = (int)fminf(fmaxf(ceilf(tile_x + trx), 0.f), fw);
-            int miny = (int)fminf(fmaxf(floorf(tile_y - try_), 0.f), fh);
-            int maxy = (int)fminf(fmaxf(ceilf(tile_y + try_), 0.f), fh);
-            ntiles = (maxy - miny) * (maxx - minx);
-            if (tile_grid != nullptr && ntiles > 0) {
-                // corner differences of the tile rectangle: a 2-D prefix sum (b200_tile_prep) turns the grid
-                // into per-tile intersection counts, i.e. the tile ranges and the radix digit histograms,
-                // without another pass over the M intersections
-                const int gs = cam.tile_w + 1;
-                atomicAdd(tile_grid + miny * gs + minx, 1);
-                atomicAdd(tile_grid + miny * gs + maxx, -1);
-                atomicAdd(tile_grid + maxy * gs + minx, -1);
-                atomicAdd(tile_grid + maxy * gs + maxx, 1);
-            }
-        } else {
-            rx = ry = 0;
         }
-        reinterpret_cast<int2*>(radii)[g] = make_int2(rx, ry);
-        float4* rec = reinterpret_cast<float4*>(splats) + 3 * g;
-        rec[0] = r0; rec[1] = r1; rec[2] = r2;
-        tiles_per_gauss[g] = ntiles;
-        if (depth_keys != nullptr) {  // split-key sort: depth digits are sorted over Gaussians, before duplication
-            depth_keys[g] = ntiles > 0 ? __float_as_uint(r2.y) : 0xFFFFFFFFu;
-            gauss_ids[g] = (int32_t)g;
-        }
+        rec[1] = r1; rec[2] = r2;
     }
     // block sum of tile counts (feeds b200_bin_scan on the 64-bit-key path; the split-key path recounts in depth order
     // and passes no buffer, which spares the CTA its closing barrier)
