@@ -60,5 +60,5 @@ class StoreAdam:
                                      self.exp_avg_sq.data_ptr(), st.flat.numel(), segs, n_seg, self.t, self.betas[0],
                                      self.betas[1], self.eps, torch.cuda.current_stream().cuda_stream), "b200_adam_step")
 
-    def zero_grad(self, set_to_none: bool = False) -> None:
-        self.store.zero_grad()
+    def zero_grad(self, set_to_none: bool = False, lazy: bool = False) -> None:
+        self.store.zero_grad(lazy=lazy)  # lazy: see GaussianStore.zero_grad

@@ -180,7 +180,9 @@ class GaussianStore(nn.Module):
         lazy=True postpones the memset: the first backward of a ``render(accumulate_grads=True)`` that runs afterwards
         WRITES the buffer (zeros for culled Gaussians and inactive SH coefficients included) and the following ones add
         to it — no 236 B/Gaussian fill and no read half of the first view's read-modify-write.  Until then the
-        ``param.grad`` views hold the previous step's values; ``flat_grad`` (property) materialises the zeros on demand."""
+        ``param.grad`` views hold the previous step's values; ``flat_grad`` (property) materialises the zeros on demand.
+        Use it only when a ``render`` backward is the first writer of the step: plain autograd contributions to a
+        ``param.grad`` (e.g. a regulariser's ``backward()``) must come after it, or they are overwritten."""
         self._attach_grads()
         if lazy:
             self._grad_state["pending_zero"] = True
