@@ -13,6 +13,7 @@ from .store import GaussianStore  # noqa: F401
 from .loss import l1_ssim_loss  # noqa: F401
 from .optim import StoreAdam  # noqa: F401
 from .streams import ViewStreams  # noqa: F401
+from . import dropin  # noqa: F401
 from .distributed import shard_views, allreduce_gradients, allreduce_flat, ViewShardedStep  # noqa: F401
 
 __all__ = [

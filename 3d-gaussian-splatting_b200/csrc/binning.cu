@@ -430,10 +430,9 @@ extern "C" int b200_tile_prep(const int32_t* tile_grid, int width, int height, i
     const int tile_w = (width + TILE - 1) / TILE, tile_h = (height + TILE - 1) / TILE;
     const size_t cells = (size_t)(tile_w + 1) * (size_t)(tile_h + 1);
     B200_REQUIRE((int64_t)tile_w * tile_h <= 65536 && cells <= b200_tile_prep_max_cells(), "tile grid too large for tile_prep");
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[B200_MAX_DEVICES] = {};
+    if (b200_first_use_on_device(attr_set)) {
         cudaFuncSetAttribute(tile_prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_set = true;
     }
     tile_prep_kernel<<<1, PREP_THREADS, cells * sizeof(int32_t), (cudaStream_t)stream>>>(tile_grid, tile_w, tile_h, offsets, total, digit_base);
     return b200_check_launch("tile_prep");

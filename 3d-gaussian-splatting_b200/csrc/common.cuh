@@ -25,6 +25,18 @@ void b200_set_error(const char* fmt, ...);
 int b200_check_launch(const char* what);
 Cam b200_make_cam(const float* cam_host, int W, int H);
 
+// cudaFuncSetAttribute is per DEVICE: a process that renders on several GPUs must set it on each.
+// Returns true exactly once per (call site's flag array, current device).
+#define B200_MAX_DEVICES 64
+static inline bool b200_first_use_on_device(bool* flags) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= B200_MAX_DEVICES) return true;  // unknown slot: set the attribute every time (harmless)
+    if (flags[dev]) return false;
+    flags[dev] = true;
+    return true;
+}
+
 #define B200_REQUIRE(cond, msg)                         \
     do {                                                \
         if (!(cond)) {                                  \

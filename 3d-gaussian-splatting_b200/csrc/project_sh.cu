@@ -742,8 +742,8 @@ static int project_fwd_impl(bool raw, const float* means, const float* quats, co
     const bool bulk = SH_BULK && sh_degree >= 0 && vec_ok != 0;
 #define FWD_ARGS means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, cam_g
 #define LAUNCH_B(D, R) do { \
-        static bool attr_set = false; \
-        if (!attr_set) { cudaFuncSetAttribute(project_sh_fwd_kernel<D, R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SH_BULK_SMEM); attr_set = true; } \
+        static bool attr_set[B200_MAX_DEVICES] = {}; \
+        if (b200_first_use_on_device(attr_set)) cudaFuncSetAttribute(project_sh_fwd_kernel<D, R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SH_BULK_SMEM); \
         project_sh_fwd_kernel<D, R, true><<<grid, block, SH_BULK_SMEM, st>>>(FWD_ARGS); } while (0)
 #define LAUNCH(D) do { if (bulk && D >= 0) { if (raw) LAUNCH_B((D < 0 ? 0 : D), true); else LAUNCH_B((D < 0 ? 0 : D), false); } \
                        else if (raw) project_sh_fwd_kernel<D, true, false><<<grid, block, 0, st>>>(FWD_ARGS); \

@@ -309,14 +309,13 @@ int sort_pairs_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_t* vals
         return B200_ESCRATCH;
     }
     cudaStream_t st = (cudaStream_t)stream;
-    static bool attr_set = false;  // one flag per template instantiation
-    if (!attr_set) {
+    static bool attr_set[B200_MAX_DEVICES] = {};  // one flag array per template instantiation, one flag per device
+    if (b200_first_use_on_device(attr_set)) {
         const int smem_max = (int)sizeof(RsSmem<KeyT>) + 160 * 1024;
         cudaFuncSetAttribute(rs_onesweep_kernel<KeyT, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
         cudaFuncSetAttribute(rs_onesweep_kernel<KeyT, 7>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
         cudaFuncSetAttribute(rs_onesweep_kernel<KeyT, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
         cudaFuncSetAttribute(rs_onesweep_kernel<KeyT, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
-        attr_set = true;
     }
     const size_t ntiles = (size_t)((M + RS_TILE - 1) / RS_TILE);
     uint32_t* hist = reinterpret_cast<uint32_t*>(scratch);

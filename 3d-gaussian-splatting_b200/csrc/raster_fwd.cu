@@ -116,10 +116,16 @@ raster_fwd_kernel(const float4* __restrict__ splats, const int32_t* __restrict__
 }  // namespace
 
 // Warps (half-tile work units) per CTA: 1, 2 or 4; overridable through the environment for tuning runs.
+// The environment is read ONCE per variable (forward / backward), not on every launch.
 int b200_ru_warps(const char* env, int dflt) {
-    const char* e = getenv(env);
-    int w = e ? atoi(e) : dflt;
-    return (w == 1 || w == 2) ? w : 4;
+    static int cached[2] = {0, 0};
+    int& c = cached[env[5] == 'B' ? 1 : 0];  // "B200_FWD_WARPS" / "B200_BWD_WARPS"
+    if (c == 0) {
+        const char* e = getenv(env);
+        const int w = e ? atoi(e) : dflt;
+        c = (w == 1 || w == 2) ? w : 4;
+    }
+    return c;
 }
 
 int b200_channels(int chset) {

@@ -81,14 +81,20 @@ def _allreduce_many(tensors: Sequence[torch.Tensor], group=None, op=dist.ReduceO
 
 
 def _views_of(flat: torch.Tensor, grads: Sequence[torch.Tensor]) -> bool:
-    """True if every gradient is a contiguous slice of ``flat`` and together they cover it in order."""
-    base, end = flat.data_ptr(), flat.data_ptr() + flat.numel() * flat.element_size()
-    total = 0
+    """True if every gradient is a contiguous, non-overlapping slice of ``flat`` (padding between slices allowed —
+    GaussianStore aligns its blocks to 16 bytes; the padding holds zeros on every rank, so reducing it is harmless)."""
+    es = flat.element_size()
+    base, end = flat.data_ptr(), flat.data_ptr() + flat.numel() * es
+    spans = []
     for g in grads:
-        if not g.is_contiguous() or g.dtype != flat.dtype or not (base <= g.data_ptr() < end):
+        if not g.is_contiguous() or g.dtype != flat.dtype:
             return False
-        total += g.numel()
-    return total <= flat.numel()
+        lo, hi = g.data_ptr(), g.data_ptr() + g.numel() * es
+        if not (base <= lo and hi <= end):
+            return False
+        spans.append((lo, hi))
+    spans.sort()
+    return all(a[1] <= b[0] for a, b in zip(spans, spans[1:]))
 
 
 class ViewShardedStep:
@@ -102,7 +108,6 @@ class ViewShardedStep:
     def __init__(self, params: Sequence[torch.Tensor], group=None):
         self.params = list(params)
         self.group = group
-        self._flat = None
 
     def __call__(self, views: Sequence, render_loss: Callable[[object], torch.Tensor]) -> float:
         world = dist.get_world_size(self.group) if dist.is_initialized() else 1
@@ -115,7 +120,7 @@ class ViewShardedStep:
             loss = render_loss(views[i])
             loss.backward()
             local_sum += float(loss.detach())
-        self._flat = allreduce_gradients(self.params, len(views), self.group, self._flat)
+        allreduce_gradients(self.params, len(views), self.group)
         t = torch.tensor([local_sum], dtype=torch.float64, device=self.params[0].device)
         if world > 1:
             dist.all_reduce(t, group=self.group)

@@ -33,6 +33,7 @@ class StoreAdam:
         self.betas, self.eps = (float(betas[0]), float(betas[1])), float(eps)
         self.exp_avg = torch.zeros_like(store.flat)
         self.exp_avg_sq = torch.zeros_like(store.flat)
+        self._generation = store.generation
         self.t = 0
 
     def _segments(self):
@@ -53,6 +54,12 @@ class StoreAdam:
     @torch.no_grad()
     def step(self) -> None:
         st = self.store
+        # the moments are laid out like `store.flat`: a store that was re-allocated without this optimiser
+        # (densify_and_prune(optimizer=None) — the reference's signature default) would be stepped out of bounds or with
+        # the wrong Gaussians' moments.  torch's Adam raises in that situation; so does this.
+        if self._generation != st.generation or self.exp_avg.numel() != st.flat.numel():
+            raise RuntimeError("StoreAdam: the store was re-allocated (densify_and_prune) without optimizer=this StoreAdam; "
+                               "pass the optimiser so its moments are spliced, or build a new StoreAdam")
         self.t += 1
         segs, n_seg = self._segments()
         with torch.cuda.device(st.flat.device):

@@ -97,7 +97,14 @@ def _pinned_scalar(dev: torch.device) -> torch.Tensor:
 
 
 def tile_n_bits(tile_w: int, tile_h: int) -> int:
+    """gsplat's key width: floor(log2(n_tiles)) + 1 — one more bit than the largest tile id needs when
+    n_tiles is a power of two (65 536 tiles -> 17)."""
     return int(math.floor(math.log2(tile_w * tile_h))) + 1
+
+
+def _tile_id_bits(n_tiles: int) -> int:
+    """Bits that actually carry tile ids 0 .. n_tiles-1 (what the 16-bit split key has to sort)."""
+    return max(1, (n_tiles - 1).bit_length())
 
 
 def _sort_scratch(M: int, dev) -> torch.Tensor:
@@ -220,7 +227,7 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
     tkeys_b = torch.empty_like(tkeys_a)
     vals_b = torch.empty_like(vals_a)
     scratch_m = _sort_scratch(M, dev)
-    tbits = tile_n_bits(tile_w, tile_h)
+    tbits = _tile_id_bits(n_tiles)  # <= 16 on this path (n_tiles <= 65 536)
     with _stage("sort_pairs"):
         if prep:
             check(lib.b200_sort_pairs_k16_prepared(_ptr(tkeys_a), _ptr(vals_a), _ptr(tkeys_b), _ptr(vals_b), M, tbits,

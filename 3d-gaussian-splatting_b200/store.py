@@ -62,6 +62,9 @@ class GaussianStore(nn.Module):
             offs[name] = o
             o += _align4(n * w)
         self._offsets, self._n = offs, n
+        # bumped on every (re-)allocation: whoever holds buffers laid out like `flat` (StoreAdam's moments, ViewStreams'
+        # accumulator nodes, optimisers built from optimizer_groups) can tell that the population changed under them
+        self.generation = getattr(self, "generation", -1) + 1
         self.flat = torch.zeros(o, dtype=torch.float32, device=dev)
         self._flat_grad = torch.zeros(o, dtype=torch.float32, device=dev)
         # shared with the backward pass (rasterization.RasterizeSplats): True after zero_grad(lazy=True) until the first
@@ -257,6 +260,7 @@ class GaussianStore(nn.Module):
                                         n_new, torch.cuda.current_stream().cuda_stream), "b200_store_gather")
         if optimizer is not None:
             optimizer.exp_avg, optimizer.exp_avg_sq = m_new, v_new
+            optimizer._generation = self.generation
         self.max_radii_2D = torch.where(keep_state.bool(), old_radii[src_rows], torch.zeros((), device=dev))
         self.xyz_gradient_accum = torch.zeros(n_new, 3, device=dev)
         self.xyz_gradient_count = torch.zeros(n_new, 1, device=dev)

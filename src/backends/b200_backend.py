@@ -6,6 +6,8 @@ packages; with this repo's root AND the reference's root on ``sys.path`` this mo
 registration point the reference has (src/gaussians/gaussian_rasterizer.py:97-118) so that
 ``backend="gsplat"`` (hard-coded at src/training/trainer.py:706-708 and src/eval.py:130) resolves to the
 B200 backend.  Do not add ``__init__.py`` under this repo's ``src/``.
+
+``python -m src.backends.b200_launch train|eval …`` runs the reference's CLI entry points on top of it.
 """
 import importlib
 import os
@@ -18,23 +20,4 @@ if _ROOT not in sys.path:
 _pkg = importlib.import_module("3d-gaussian-splatting_b200")
 B200Backend = _pkg.B200Backend
 rasterization = _pkg.rasterization
-
-
-def register():
-    """Make the reference's GaussianRasterizer pick B200Backend for backend in {"gsplat","b200","auto"}."""
-    import types
-
-    if "gsplat" not in sys.modules:  # the reference imports `from gsplat import rasterization` at module top
-        shim = types.ModuleType("gsplat")
-        shim.rasterization = rasterization
-        shim.__version__ = "b200-shim"
-        sys.modules["gsplat"] = shim
-    gr = importlib.import_module("src.gaussians.gaussian_rasterizer")
-
-    def _initialize_backend(self, backend, K):
-        if backend in ("auto", "gsplat", "b200"):
-            return B200Backend(K)
-        raise RuntimeError("No rasterization backend available!")
-
-    gr.GaussianRasterizer._initialize_backend = _initialize_backend
-    return gr
+register = _pkg.dropin.register  # shims for absent modules + the registration patch (dropin.py)

@@ -1,0 +1,100 @@
+"""Shared pieces of the GPU parity tests: camera / intrinsics variants and the tolerance criteria.
+
+Cameras: the reference hands the backend arbitrary world->camera poses (src/training/trainer.py:459-466) and ONE
+shared pinhole ``K`` (src/backends/gsplat_backend.py:175) — so every direct CUDA-vs-oracle comparison runs on
+  "identity"   viewmat = I4, fx = fy, cx = W/2, cy = H/2   (SURVEY §8d's view 0)
+  "posed"      a camera with yaw + pitch + roll and a translation (R, t, campos = -R^T t all non-trivial)
+  "asymK"      the posed camera with fx != fy, cx != W/2, cy != H/2
+
+Gradient criterion (BASELINE.json north_star: "relative error <= 1e-3 on parameter gradients"), per GAUSSIAN rather
+than per tensor: row i of an attribute passes when  max_j |g_ij - ref_ij| <= 1e-3 * max(max_j |ref_ij|, 1e-3 * ||ref||_inf).
+At least 99.9 % of the rows must pass and no row may be off by more than 2 % of the attribute's largest gradient
+(rows that fail sit on a discrete decision — a ceil() of the radius, the alpha >= 1/255 test, the T <= 1e-4 stop —
+that two floating-point implementations legitimately take differently; their count and the worst row are printed).
+
+Image criterion: max-abs <= 1e-4 on every pixel except those where a skip / stop decision lies within rounding of its
+threshold ("marginal"); those are bounded in number (fraction printed) and in size (<= 0.05).
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+CAMS = ("identity", "posed", "asymK")
+
+
+def pose(kind: str) -> torch.Tensor:
+    if kind == "identity":
+        return torch.eye(4)
+    yaw, pitch, roll = 0.09, -0.06, 0.21
+    cy, sy, cp, sp, cr, sr = math.cos(yaw), math.sin(yaw), math.cos(pitch), math.sin(pitch), math.cos(roll), math.sin(roll)
+    Ry = torch.tensor([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]], dtype=torch.float64)
+    Rx = torch.tensor([[1, 0, 0], [0, cp, -sp], [0, sp, cp]], dtype=torch.float64)
+    Rz = torch.tensor([[cr, -sr, 0], [sr, cr, 0], [0, 0, 1]], dtype=torch.float64)
+    R = Rz @ Rx @ Ry
+    pos = torch.tensor([0.35, -0.2, -0.4], dtype=torch.float64)  # camera centre in world coordinates
+    m = torch.eye(4, dtype=torch.float64)
+    m[:3, :3] = R
+    m[:3, 3] = -R @ pos
+    return m.to(torch.float32)
+
+
+def intrinsics(kind: str, K: torch.Tensor, W: int, H: int) -> torch.Tensor:
+    if kind != "asymK":
+        return K
+    K = K.clone()
+    K[1, 1] = 0.83 * K[0, 0]
+    K[0, 2] = 0.46 * W
+    K[1, 2] = 0.57 * H
+    return K
+
+
+def apply_camera(sc: dict, kind: str, W: int, H: int) -> dict:
+    sc = dict(sc)
+    sc["viewmat"] = pose(kind)
+    sc["K"] = intrinsics(kind, sc["K"], W, H)
+    return sc
+
+
+def grad_rows(got: torch.Tensor, ref: torch.Tensor, name: str, rtol: float = 1e-3, floor: float = 1e-3,
+              min_ok: float = 0.999, cap: float = 2e-2) -> dict:
+    """Per-Gaussian gradient criterion (see the module docstring).  Returns the measured figures; asserts the bars."""
+    n = ref.shape[0]
+    g, r = got.detach().reshape(n, -1).double().cpu(), ref.detach().reshape(n, -1).double().cpu()
+    assert torch.isfinite(g).all(), f"{name}: non-finite gradient"
+    scale = r.abs().amax().clamp_min(1e-300)
+    tol = rtol * torch.maximum(r.abs().amax(1), floor * scale)
+    err = (g - r).abs().amax(1)
+    ok = err <= tol
+    frac = ok.double().mean().item()
+    worst = int(torch.argmax(err / tol))
+    l2 = ((g - r).norm() / r.norm().clamp_min(1e-300)).item()
+    out = dict(name=name, rows=n, frac_ok=frac, worst_row=worst, worst_err=err[worst].item(), worst_ref=r[worst].abs().amax().item(),
+               worst_abs_over_scale=(err.amax() / scale).item(), l2_rel=l2)
+    print(f"grad[{name}]: {frac * 100:.4f} % of {n} rows within 1e-3; worst row {worst}: err {out['worst_err']:.3e} vs |ref| "
+          f"{out['worst_ref']:.3e}; max err / ||ref||_inf {out['worst_abs_over_scale']:.2e}; whole-tensor L2-rel {l2:.2e}")
+    assert frac >= min_ok, f"{name}: only {frac * 100:.3f} % of rows within {rtol} (need {min_ok * 100} %)"
+    assert out["worst_abs_over_scale"] <= cap, f"{name}: worst row off by {out['worst_abs_over_scale']:.3e} of the attribute's max"
+    assert l2 <= rtol, f"{name}: whole-tensor relative error {l2}"
+    return out
+
+
+def image_close(got: torch.Tensor, ref: torch.Tensor, marginal=None, tol: float = 1e-4, max_marginal: float = 0.02,
+                cap: float = 0.05, what: str = "render") -> dict:
+    """`marginal` = the oracle's mask of threshold-tied pixels, or None when the checker cannot provide one (C port):
+    then at most `max_marginal` of the pixels may exceed `tol`.  Either way no pixel may be off by more than `cap`."""
+    err = (got.detach().cpu() - ref.detach().cpu()).abs().amax(-1)
+    over = err > tol
+    if marginal is not None:
+        bad = (over & ~marginal).float().mean().item()
+        frac = marginal.float().mean().item()
+        assert bad == 0.0, f"{what}: {bad:.2e} of the non-marginal pixels exceed {tol} (max {err[~marginal].max().item():.3e})"
+    else:
+        frac = over.float().mean().item()
+    print(f"image[{what}]: max err {err.max().item():.3e}, median {err.median().item():.2e}, pixels above {tol}: "
+          f"{over.float().mean().item():.3e}, excluded fraction {frac:.3e}")
+    assert frac <= max_marginal, f"{what}: {frac:.3e} of the pixels excluded / above {tol}"
+    assert err.max().item() <= cap, f"{what}: worst pixel off by {err.max().item():.3e} (cap {cap})"
+    assert err.median().item() <= 2e-6
+    return dict(max=err.max().item(), frac_over=over.float().mean().item())

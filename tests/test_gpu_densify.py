@@ -136,3 +136,69 @@ def test_densify_and_prune_matches_reference_bookkeeping(pkg, oracle, N, cap):
         res["render"].sum().backward()
         opt.step()
         assert torch.isfinite(st.flat).all()
+
+
+# ------------------------------------------------------------------------------------------------------------
+# the same check against the reference's OWN GaussianModel + torch Adam (src/gaussians/gaussian_model.py:53-366 run as
+# shipped on CUDA; optimiser groups from GaussianTrainer._setup_optimizer, trainer.py:331-340) — VERDICT r1 item 3b.
+# The restatement above stays as a second opinion.
+# ------------------------------------------------------------------------------------------------------------
+from dropin_harness import reference, reference_available  # noqa: E402
+
+needs_reference = pytest.mark.skipif(not reference_available(), reason="reference tree not staged (baseline/stage_reference.py)")
+
+
+def _reference_model_with_state(oracle, N, seed):
+    gr, tr, gm, cfg = reference()
+    sc = oracle.synthetic_scene(N, 320, 200, seed=seed)
+    model = gm.GaussianModel(n_gaussians=N, device=DEV)
+    with torch.no_grad():
+        for a in ATTRS:
+            getattr(model, a).data = sc[a].to(DEV).clone()
+    trainer = tr.GaussianTrainer(cfg.TrainingConfig(), device=DEV, wandb_run=None)
+    opt = trainer._setup_optimizer(model)
+    for a in ATTRS:  # materialise Adam's per-parameter state (zero gradient, zero moments: parameters do not move)
+        getattr(model, a).grad = torch.zeros_like(getattr(model, a))
+    opt.step()
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    for a in ATTRS:
+        st = opt.state[getattr(model, a)]
+        st["exp_avg"].copy_(torch.randn(st["exp_avg"].shape, generator=g, device=DEV))
+        st["exp_avg_sq"].copy_(torch.rand(st["exp_avg_sq"].shape, generator=g, device=DEV))
+    model.xyz_gradient_accum = torch.rand(N, 3, generator=g, device=DEV) * 4e-4
+    model.xyz_gradient_count = torch.randint(0, 5, (N, 1), generator=g, device=DEV).float()
+    model.max_radii_2D = torch.rand(N, generator=g, device=DEV)
+    return model, opt
+
+
+@needs_reference
+@pytest.mark.parametrize("N,cap", [(20000, None), (20000, 20500), (20000, 20000), (3000, None), (1, None), (50000, 52000)])
+def test_densify_and_prune_matches_the_reference_model(pkg, oracle, N, cap):
+    model, ref_opt = _reference_model_with_state(oracle, N, seed=31)
+    st = pkg.GaussianStore.from_tensors(*(getattr(model, a).detach().clone() for a in
+                                          ("xyz", "features_dc", "features_rest", "scaling", "rotation", "opacity")))
+    lrs = {"xyz": 1.6e-4, "f_dc": 0.0025, "f_rest": 1.25e-4, "opacity": 0.05, "scaling": 0.005, "rotation": 0.001}
+    opt = pkg.StoreAdam(st, lrs)
+    m0, v0 = _moments(st, opt.exp_avg), _moments(st, opt.exp_avg_sq)
+    for a in ATTRS:
+        m0[a].copy_(ref_opt.state[getattr(model, a)]["exp_avg"])
+        v0[a].copy_(ref_opt.state[getattr(model, a)]["exp_avg_sq"])
+    st.xyz_gradient_accum.copy_(model.xyz_gradient_accum)
+    st.xyz_gradient_count.copy_(model.xyz_gradient_count)
+    st.max_radii_2D.copy_(model.max_radii_2D)
+    kw = dict(grads_threshold=2e-4, min_opacity=0.05, extent=0.2, max_screen_size=12.0, max_gaussians=cap)
+    torch.manual_seed(1234)
+    want = model.densify_and_prune(optimizer=ref_opt, **kw)
+    torch.manual_seed(1234)
+    got = st.densify_and_prune(optimizer=opt, **kw)
+    assert got == want, (got, want)  # the whole statistics dict, incl. pruned_low_op / pruned_too_big / capped
+    if N > 1000 and cap is None:
+        assert want["cloned"] > 0 and want["split"] > 0 and want["pruned"] > 0
+    m, v = _moments(st, opt.exp_avg), _moments(st, opt.exp_avg_sq)
+    for a in ATTRS:
+        p = getattr(model, a)
+        assert torch.equal(getattr(st, a).detach(), p.detach()), a
+        assert torch.equal(m[a], ref_opt.state[p]["exp_avg"]) and torch.equal(v[a], ref_opt.state[p]["exp_avg_sq"]), a
+        assert any(q is p for grp in ref_opt.param_groups for q in grp["params"])
+    assert torch.equal(st.xyz_gradient_accum, model.xyz_gradient_accum) and torch.equal(st.xyz_gradient_count, model.xyz_gradient_count)
+    assert torch.equal(st.max_radii_2D, model.max_radii_2D)

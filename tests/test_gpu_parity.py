@@ -11,13 +11,16 @@ import math
 import pytest
 import torch
 
+from parity_util import CAMS, apply_camera, grad_rows, image_close
+
 pytestmark = pytest.mark.gpu
 
 DEV = "cuda"
 
 
-def _scene(oracle, N, W, H, seed=0):
-    sc = oracle.synthetic_scene(N, W, H, seed=seed)
+def _scene(oracle, N, W, H, seed=0, cam="identity"):
+    """`cam`: "identity" | "posed" (rotated + translated w2c) | "asymK" (posed, fx != fy, off-centre principal point)."""
+    sc = apply_camera(oracle.synthetic_scene(N, W, H, seed=seed), cam, W, H)
     act = oracle.activate(sc)
     return sc, act
 
@@ -52,10 +55,11 @@ def _gpu_full(pkg, act, sc, W, H, deg, mode="RGB", bg=None, requires_grad=False)
 # ------------------------------------------------------------------------------------------------
 # stage 1: projection + SH
 # ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("cam", CAMS)
 @pytest.mark.parametrize("deg", [0, 1, 2, 3])
-def test_projection_and_sh_match_oracle(pkg, oracle, deg):
+def test_projection_and_sh_match_oracle(pkg, oracle, deg, cam):
     N, W, H = 20000, 320, 192
-    sc, act = _scene(oracle, N, W, H)
+    sc, act = _scene(oracle, N, W, H, cam=cam)
     proj = oracle.project(act["means3D"], act["rotations"], act["scales"], act["opacities"].squeeze(-1),
                           sc["viewmat"], sc["K"], W, H)
     vis_o = (proj["radii"] > 0).all(-1)
@@ -125,11 +129,13 @@ def test_sh_row_fetch_paths_agree(pkg, oracle, deg, shift):
 # ------------------------------------------------------------------------------------------------
 # stage 2: binning / sort / ranges — bit exact
 # ------------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("N,W,H", [(3000, 160, 96), (50000, 640, 360), (20000, 1920, 1080), (30000, 3840, 2160)])
-def test_split_key_binning_bit_exact(pkg, oracle, N, W, H):
+@pytest.mark.parametrize("N,W,H,cam", [(3000, 160, 96, "identity"), (50000, 640, 360, "identity"), (20000, 1920, 1080, "identity"),
+                                       (30000, 3840, 2160, "identity"), (50000, 640, 360, "asymK"), (20000, 1920, 1080, "posed"),
+                                       (20000, 4096, 4096, "identity")])  # exactly 65 536 tiles: 16-bit ids, gsplat's key width 17
+def test_split_key_binning_bit_exact(pkg, oracle, N, W, H, cam):
     """Fast path (depth digits sorted over Gaussians, 16-bit tile digits over intersections) must give the
     same sorted keys / ids / ranges as a stable sort of the 64-bit keys."""
-    sc, act = _scene(oracle, N, W, H, seed=3)
+    sc, act = _scene(oracle, N, W, H, seed=3, cam=cam)
     a = _cuda(act)
     cam = pkg.make_cam(sc["viewmat"], sc["K"], W, H)
     b = pkg.project_and_bin(a["means3D"], a["rotations"], a["scales"], a["opacities"].squeeze(-1).contiguous(),
@@ -289,18 +295,15 @@ def test_sort_scratch_too_small_is_an_error(pkg):
 # stage 3: forward blend
 # ------------------------------------------------------------------------------------------------
 def _assert_image_close(got, ref, marginal, tol=1e-4):
-    err = (got - ref).abs().amax(-1)
-    ok = ~marginal if marginal is not None else torch.ones_like(err, dtype=torch.bool)
-    assert err[ok].max().item() <= tol, f"max abs err {err[ok].max().item()} on non-marginal pixels"
-    if marginal is not None:
-        # a pixel whose skip/stop decision sits within fp32 rounding of its threshold may differ by one term
-        assert marginal.float().mean().item() < 0.02
-        assert err.max().item() < 0.05
+    # max-abs <= 1e-4 off the oracle's mask of threshold-tied pixels; the mask is bounded in size (2 %) and the error on it
+    # is capped (0.05: one Gaussian's contribution) — parity_util.image_close
+    image_close(got, ref, marginal, tol=tol)
 
 
+@pytest.mark.parametrize("cam", CAMS)
 @pytest.mark.parametrize("N,W,H,deg", [(4000, 160, 96, 3), (30000, 320, 200, 3), (4000, 150, 90, 1)])
-def test_forward_render_matches_oracle(pkg, oracle, N, W, H, deg):
-    sc, act = _scene(oracle, N, W, H, seed=1)
+def test_forward_render_matches_oracle(pkg, oracle, N, W, H, deg, cam):
+    sc, act = _scene(oracle, N, W, H, seed=1, cam=cam)
     bg = torch.tensor([0.2, 0.5, 0.7])
     r_o, a_o, m_o = _oracle_full(oracle, act, sc, W, H, deg, bg=bg, margin=1e-3)
     r_g, a_g, meta, _ = _gpu_full(pkg, act, sc, W, H, deg, bg=bg)
@@ -359,11 +362,12 @@ def _rel(got, ref):
     return ((got - ref).norm() / ref.norm().clamp_min(1e-12)).item()
 
 
+@pytest.mark.parametrize("cam", CAMS)
 @pytest.mark.parametrize("N,W,H,deg,mode", [(3000, 128, 80, 3, "RGB"), (3000, 128, 80, 2, "RGB"),
                                             (12000, 240, 136, 3, "RGB"), (3000, 128, 80, 3, "RGB+ED"),
                                             (3000, 128, 80, 0, "RGB+D")])
-def test_gradients_match_oracle_autograd(pkg, oracle, N, W, H, deg, mode):
-    sc, act = _scene(oracle, N, W, H, seed=7)
+def test_gradients_match_oracle_autograd(pkg, oracle, N, W, H, deg, mode, cam):
+    sc, act = _scene(oracle, N, W, H, seed=7, cam=cam)
     bg = torch.tensor([0.3, 0.1, 0.6])
     nch = 3 if mode == "RGB" else 4
     gen = torch.Generator().manual_seed(1)
@@ -388,14 +392,12 @@ def test_gradients_match_oracle_autograd(pkg, oracle, N, W, H, deg, mode):
         loss_g = loss_g + (a_g * v_alpha.to(DEV)).sum()
     loss_g.backward()
 
-    # the comparison is only meaningful if both made the same discrete decisions (same binning)
-    same = torch.equal(meta["radii"][0].cpu(), m_o["radii"])
+    # per-Gaussian criterion (parity_util.grad_rows): >= 99.9 % of the rows within 1e-3, worst row capped, and the
+    # whole-tensor relative error <= 1e-3 — with no looser fallback when a radius differs somewhere
+    print(f"radii identical to the fp64 oracle: {torch.equal(meta['radii'][0].cpu(), m_o['radii'])}")
     for k in ("means3D", "rotations", "scales", "opacities", "shs"):
-        go = leaves_o[k].grad.float().reshape(leaves_g[k].shape)
-        gg = leaves_g[k].grad.cpu()
-        assert torch.isfinite(gg).all()
-        rel = _rel(gg, go)
-        assert rel <= (1e-3 if same else 2e-2), f"{k}: relative gradient error {rel} (same radii: {same})"
+        go = leaves_o[k].grad.reshape(leaves_g[k].shape)
+        grad_rows(leaves_g[k].grad, go, f"{k}/{mode}/deg{deg}/{cam}")
     # SH coefficients above the active degree get exactly zero gradient (trainer.py:77-87 schedule)
     nb = (deg + 1) ** 2
     assert (leaves_g["shs"].grad[:, nb:, :] == 0).all()

@@ -27,16 +27,30 @@ def _viewpoint(sc, W, H, viewmat=None):
 
 
 def _reference_chain(pkg, sc, W, H, deg, v, viewmats):
-    """raw leaves -> reference getters -> unfused backend -> autograd; returns image of the last view and raw grads."""
-    raw = {k: sc[k].to(DEV).clone().requires_grad_(True)
-           for k in ("xyz", "features_dc", "features_rest", "scaling", "rotation", "opacity")}
+    """raw leaves -> reference getters -> unfused backend -> autograd; returns image of the last view and raw grads.
+    The getters are the reference's OWN `GaussianModel` properties (src/gaussians/gaussian_model.py:90-108) and the input
+    dict its `GaussianTrainer._gaussian_params` (trainer.py:399-406) whenever the reference tree is staged; the
+    restatement below is the fallback."""
+    from dropin_harness import reference, reference_available
+    keys = ("xyz", "features_dc", "features_rest", "scaling", "rotation", "opacity")
+    model = trainer = None
+    if reference_available():
+        gr, tr, gm, cfg = reference()
+        model = gm.GaussianModel(n_gaussians=sc["xyz"].shape[0], device=DEV)
+        for k in keys:
+            getattr(model, k).data = sc[k].to(DEV).clone()
+        trainer = tr.GaussianTrainer(cfg.TrainingConfig(), device=DEV, wandb_run=None)
+        raw = {k: getattr(model, k) for k in keys}
+    else:
+        raw = {k: sc[k].to(DEV).clone().requires_grad_(True) for k in keys}
     be = pkg.B200Backend(sc["K"].to(DEV))
     img = None
     for vm in viewmats:
-        params = {"means3D": raw["xyz"], "scales": torch.exp(raw["scaling"]),
-                  "rotations": torch.nn.functional.normalize(raw["rotation"], dim=-1),
-                  "opacities": torch.sigmoid(raw["opacity"]),
-                  "shs": torch.cat([raw["features_dc"], raw["features_rest"]], dim=1)}
+        params = trainer._gaussian_params(model) if model is not None else {
+            "means3D": raw["xyz"], "scales": torch.exp(raw["scaling"]),
+            "rotations": torch.nn.functional.normalize(raw["rotation"], dim=-1),
+            "opacities": torch.sigmoid(raw["opacity"]),
+            "shs": torch.cat([raw["features_dc"], raw["features_rest"]], dim=1)}
         res = be.render_with_depth(params, _viewpoint(sc, W, H, vm), bg_color=torch.zeros(3, device=DEV),
                                    render_mode="RGB", device="cuda", sh_degree=deg)
         img = res["render"]
