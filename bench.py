@@ -44,6 +44,33 @@ def metric_name(config: str) -> str:
 LAST_PAIRS = None  # (pixel x Gaussian pairs visited, composited) by the CPU port's last forward blend
 
 
+def config_dict(name: str, V: int, n_vis, M, world: int = 1, total_views: int = 0) -> dict:
+    """The `config` object — identical on the B200 arm and the `--impl reference` arm for the same flags."""
+    N, W, H, deg = CONFIGS[name]
+    return {"workload": f"{name}: {N} gaussians SH{deg}, {W}x{H}, {V} view(s)/rank/step fwd+bwd, cameras = circle_cameras(64)",
+            "N": N, "N_visible": n_vis, "M_isects": M, "views_per_rank": V,
+            "l2": "inputs larger than L2 (params 236 B/Gaussian + keys/records per view > 126 MB); no explicit flush"}
+
+
+def view_index(step: int, v: int, V: int, rank: int = 0, world: int = 1) -> int:
+    """Camera of view `v` of step `step` on `rank` (same sequence on both arms)."""
+    return (step * world * V + rank * V + v) % 64
+
+
+def gsplat_probe() -> str:
+    """is the reference's real arithmetic provider (gsplat==1.5.3, requirements.txt:9) importable here?"""
+    import importlib.util
+    try:
+        if importlib.util.find_spec("gsplat") is None:
+            return "gsplat unavailable on this box"
+        import gsplat
+        if getattr(gsplat, "__version__", "") == "b200-shim":
+            return "gsplat unavailable on this box"
+        return f"gsplat {gsplat.__version__} importable (pin: tests/test_gpu_gsplat_pin.py)"
+    except Exception as e:
+        return f"gsplat unavailable on this box (import failed: {type(e).__name__})"
+
+
 def _peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -126,9 +153,9 @@ class StageTimer:
 # ---------------------------------------------------------------------------------------------------
 # CPU arm: the oracle's C/OpenMP port (oracle/cpu_splat.c -> oracle/_cpu/libcpusplat.so)
 # ---------------------------------------------------------------------------------------------------
-def cpu_port_time(N, W, H, deg, steps, warmup, seed=0):
-    """Times fwd+bwd of one view on the host cores with the C port of the oracle.  Returns
-    (seconds_per_view, cores, M) or raises if the port is not built."""
+def cpu_port_time(N, W, H, deg, steps, warmup, seed=0, views_per_step=1):
+    """Times fwd+bwd of `views_per_step` views per step on the host cores with the C port of the oracle (same scene,
+    same camera sequence as the B200 arm).  Returns (seconds_per_step, cores, M of camera 0, N_visible of camera 0)."""
     from oracle import cpu_port
     import torch
     from oracle import torch_oracle as orc
@@ -136,19 +163,23 @@ def cpu_port_time(N, W, H, deg, steps, warmup, seed=0):
     cpu_port.set_threads(os.cpu_count() or 1)  # all host cores, whatever OMP_NUM_THREADS the launcher exported
     sc = orc.synthetic_scene(N, W, H, seed=seed)
     act = orc.activate(sc)
+    cams = orc.circle_cameras(64)
     g = torch.Generator().manual_seed(1)
     v_render = torch.randn(H, W, 3, generator=g)
-    times, M = [], 0
-    for i in range(warmup + steps):
-        t0 = time.perf_counter()
-        out = cpu_port.forward_backward(act, sc["viewmat"], sc["K"], W, H, deg, v_render)
-        dt = time.perf_counter() - t0
-        M = out["M"]
-        if i >= warmup:
-            times.append(dt)
+    fw0 = cpu_port.forward(act, cams[0], sc["K"], W, H, deg, bg=torch.zeros(3))
+    M0, nvis0 = fw0["M"], int((fw0["radii"] > 0).all(-1).sum())
     global LAST_PAIRS
     LAST_PAIRS = cpu_port.pairs_evaluated()
-    return sum(times) / len(times), cpu_port.num_threads(), M
+    del fw0
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        for v in range(views_per_step):
+            cpu_port.forward_backward(act, cams[view_index(i, v, views_per_step)], sc["K"], W, H, deg, v_render)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    return sum(times) / len(times), cpu_port.num_threads(), M0, nvis0
 
 
 def run_reference(args):
@@ -156,24 +187,32 @@ def run_reference(args):
     if rank != 0:
         return 0
     N, W, H, deg = CONFIGS[args.config]
-    # bounded sample: the SAME workload (full N, full resolution), one view per step, few steps
-    steps = max(1, min(args.steps, 3))
-    warm = 1 if args.warmup > 0 else 0
+    V = args.views_per_rank if not args.total_views else max(1, args.total_views // max(1, args.gpus))
+    # the SAME workload as the B200 arm — full N, full resolution, the same cameras, V views per step, exactly K timed steps
+    # after W warm-up steps — unless that would take more than a few minutes on the host cores (config C / B at size):
+    # then the step count is bounded (one view of config A is ~0.3-0.6 s on 16-32 threads)
+    steps, warm = max(1, args.steps), max(0, args.warmup)
+    budget_views = 160 if args.config in ("A", "tiny") else 24
+    if (steps + warm) * V > budget_views:
+        steps = max(1, budget_views // V - min(warm, 1))
+        warm = min(warm, 1)
     try:
-        sec, cores, M = cpu_port_time(N, W, H, deg, steps, warm)
+        sec, cores, M, nvis = cpu_port_time(N, W, H, deg, steps, warm, views_per_step=V)
     except Exception as e:  # the port is part of the repo; failing to run it is an error worth seeing
         print(json.dumps({"impl": "reference", "unavailable": f"oracle C port failed: {e!r}"[:200]}))
         return 0
-    mpix = W * H / sec / 1e6
+    mpix = V * W * H / sec / 1e6
     line = {
         "impl": "reference", "metric": metric_name(args.config), "value": mpix, "unit": "Mpix/s", "n_gpus": args.gpus, "steps": steps,
-        "warmup": warm, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.config}: {N} gaussians SH{deg}, {W}x{H}, 1 view fwd+bwd per step, CPU"},
+        "warmup": warm, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong" if args.total_views else "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": config_dict(args.config, V, nvis, M, args.gpus, args.total_views),
         "cpu_baseline": {"value": mpix, "unit": "Mpix/s", "cores": cores, "kind": "port",
-                         "sample": f"{steps} full views (N={N}, {W}x{H}, M={M}) on {cores} host threads, oracle/cpu_splat.c"},
+                         "sample": f"{steps} steps x {V} full views (N={N}, {W}x{H}, M={M} at camera 0) on {cores} host threads, "
+                                   "oracle/cpu_splat.c (the reference has no CPU implementation of this path: "
+                                   "src/backends/pytorch_backend.py:1-5 raises)"},
         "e2e": {"value": mpix, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
+        "gpu_launches": 0, "oracle_pin": gsplat_probe(),
     }
     print(json.dumps(line))
     return 0
@@ -225,14 +264,21 @@ def run_b200(args):
     # drain phase of one view run under the long blend kernels of the other
     vstreams = pkg.ViewStreams(dev, args.view_streams, params_list)
 
-    def view_index(step, v):
-        return (step * world * V + rank * V + v) % 64
+    _vi = view_index
+
+    def view_index(step, v):  # noqa: F811 — this rank's camera sequence
+        return _vi(step, v, V, rank, world)
+
+    probe = {"on": False, "render": [], "reduce": []}  # CUDA events of the multi-GPU diagnostic pass (not the headline)
 
     def step_device(step):
         """inputs resident in HBM: pose + cotangent on device."""
         nonlocal flat
         for p in params_list:
             p.grad = None
+        if probe["on"]:
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            ev[0].record()
         vstreams.begin()
         for v in range(V):
             with vstreams.view(v):
@@ -240,8 +286,14 @@ def run_b200(args):
                 res = backend.render_with_depth(leaves, vp, bg_color=bg, render_mode="RGB", device="cuda", sh_degree=deg)
                 res["render"].backward(v_render)
         vstreams.join()
+        if probe["on"]:
+            ev[1].record()
         if world > 1:
             flat = pkg.allreduce_gradients(params_list, world * V, flat=flat)
+        if probe["on"]:
+            ev[2].record()
+            probe["render"].append((ev[0], ev[1]))
+            probe["reduce"].append((ev[1], ev[2]))
 
     # e2e: every view's pose and ground-truth frame come from pinned HOST memory.  The upload of view k+1 runs
     # on a copy stream while view k renders (double-buffered device slots, events both ways), as a training loop
@@ -384,14 +436,35 @@ def run_b200(args):
     if rank == 0:
         sampler.start()
     ms_dev, launches = timed(step_device, args.steps, args.warmup, timer)
-    timer_one = None
-    if args.view_streams > 1:  # per-stage durations without the other view's kernels in between (not the headline)
+    timer_one, ms_one = None, None
+    if args.view_streams > 1:
+        # the same K steps on ONE stream — what a caller that syncs between views (the unmodified reference trainer,
+        # trainer.py:495-497) can get; also gives per-stage durations without the other view's kernels in between
         multi, vstreams = vstreams, pkg.ViewStreams(dev, 1)
         timer_one = StageTimer(torch)
         pkg._lib.stage_timer = timer_one
-        timed(step_device, max(2, args.steps // 4), 1, timer_one)
+        ms_one, _ = timed(step_device, args.steps, 3, timer_one)
         vstreams = multi
         pkg._lib.stage_timer = timer
+    # multi-GPU diagnostic pass: where does the step go beyond one rank's render?  (a) the collective itself, (b) waiting
+    # for the slowest rank.  Events bracket this rank's render and its all-reduce; the collective cannot start before the
+    # slowest rank arrives, so the MIN over ranks of the reduce bracket is the collective alone and max-min of the render
+    # bracket is the spread.
+    multi_gpu = None
+    if world > 1:
+        probe["on"] = True
+        timed(step_device, args.steps, 2)
+        probe["on"] = False
+        r_ms = sum(a.elapsed_time(b) for a, b in probe["render"][2:]) / max(1, len(probe["render"]) - 2)
+        c_ms = sum(a.elapsed_time(b) for a, b in probe["reduce"][2:]) / max(1, len(probe["reduce"]) - 2)
+        t = torch.tensor([r_ms, -r_ms, c_ms, -c_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        r_max, r_min, c_max, c_min = float(t[0]), -float(t[1]), float(t[2]), -float(t[3])
+        multi_gpu = {"render_ms_max": round(r_max, 4), "render_ms_min": round(r_min, 4), "rank_spread_ms": round(r_max - r_min, 4),
+                     "allreduce_ms": round(c_min, 4), "allreduce_bracket_ms_max": round(c_max, 4),
+                     "allreduce_bytes": int(sum(p.numel() for p in params_list) * 4),
+                     "note": "allreduce_ms = min over ranks of the bracket around the collective (the last rank to arrive waits "
+                             "for nobody); rank_spread_ms = max - min over ranks of the per-step render time"}
     ms_e2e, _ = timed(step_e2e, args.steps, max(1, args.warmup // 2))
     ms_store, _ = timed(step_store, args.steps, max(1, args.warmup // 2))
     ms_train, _ = timed(step_train, args.steps, max(1, args.warmup // 2))
@@ -400,13 +473,46 @@ def run_b200(args):
         sampler.join(timeout=2)
     pkg._lib.stage_timer = None
 
-    # scene statistics for the last view (N_visible, M) and the per-stage roofline
+    # scene statistics for camera 0 (N_visible, M) and the per-stage roofline
     with torch.no_grad():
         cam = pkg.make_cam(poses_dev[0], K, W, H)
         b = pkg.project_and_bin(leaves["means3D"], leaves["rotations"], leaves["scales"],
                                 leaves["opacities"].squeeze(-1).contiguous(), leaves["shs"], deg, cam, W, H)
         M = b["M"]
         n_vis = int((b["radii"] > 0).all(-1).sum().item())
+        del b, cam
+
+    # The reference's OWN training step, unmodified (src/training/trainer.py:447-519 as written: getters, autocast,
+    # render_with_depth, _stclamp, L1 + five avg_pool2d, three .item() per view, scale regulariser, GradScaler, torch Adam
+    # over the six groups), with B200Backend registered behind GaussianRasterizer — one stream, batch_size views, this
+    # config's scene.  N=1 only (the reference has no distributed code); needs the staged reference tree.
+    ref_trainer = None
+    if world == 1 and not args.no_reference_trainer:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            import dropin_harness as dh
+            if not dh.reference_available():
+                raise LookupError("reference tree not staged (baseline/stage_reference.py runs in the build container)")
+            start = {k: sc[k] for k in dh.KEYS}
+            trainer, model, opt, rast = dh.make_trainer(start, sc["K"], "cuda", batch_size=V)
+            trainer.iteration = 10 ** 6  # SH schedule saturated: degree 3, as in every other leg
+            assert isinstance(rast.backend, pkg.B200Backend)
+            gts = [torch.rand(H, W, 3, generator=gen) for _ in range(2)]
+            tviews = dh.tensor_views([cams[i] for i in range(64)], [gts[i & 1] for i in range(64)], sc["K"], W, H, "cuda")
+
+            def step_ref(step):
+                trainer._training_step(model, rast, [tviews[view_index(step, v)] for v in range(V)], opt)
+
+            ms_ref, ref_launches = timed(step_ref, args.steps, 3)
+            ref_trainer = {"it_per_s": 1e3 / (ms_ref / args.steps), "ms_per_step": ms_ref / args.steps,
+                           "Mpix_per_s": V * W * H / (ms_ref / args.steps / 1e3) / 1e6, "views_per_step": V,
+                           "b200_kernels_per_step": ref_launches / args.steps,
+                           "what": "UNMODIFIED GaussianTrainer._training_step (trainer.py:447-519) + GaussianModel + torch Adam + "
+                                   "GradScaler from the staged reference tree, B200Backend registered at "
+                                   "gaussian_rasterizer.py:97-118; one stream, host sync every view (.item())"}
+        except Exception as e:
+            ref_trainer = {"it_per_s": None, "unavailable": f"{type(e).__name__}: {e}"[:200]}
+
     views_total = args.steps * V
     pix_per_step = world * V * W * H
     value = pix_per_step / (ms_dev / args.steps / 1e3) / 1e6
@@ -466,9 +572,9 @@ def run_b200(args):
         if world > 1:  # the CPU baseline is measured on rank 0 at N=1 only
             raise LookupError("not measured at N>1 (see the N=1 line)")
         # bounded sample of the same workload on the host cores: one full view, C/OpenMP port of the oracle
-        sec, cores, Mc = cpu_port_time(N, W, H, deg, steps=1, warmup=0)
-        cpu_baseline = {"value": W * H / sec / 1e6, "unit": "Mpix/s", "cores": cores, "kind": "port",
-                        "sample": f"1 full view fwd+bwd (N={N}, {W}x{H}, M={Mc}), oracle/cpu_splat.c OpenMP",
+        sec, cores, Mc, _ = cpu_port_time(N, W, H, deg, steps=2, warmup=1, views_per_step=V if args.config in ("A", "tiny") else 1)
+        cpu_baseline = {"value": (V if args.config in ("A", "tiny") else 1) * W * H / sec / 1e6, "unit": "Mpix/s", "cores": cores, "kind": "port",
+                        "sample": f"2 steps x {V if args.config in ('A', 'tiny') else 1} full view(s) fwd+bwd after 1 warm-up step (N={N}, {W}x{H}, M={Mc} at camera 0), oracle/cpu_splat.c OpenMP",
                         "P_pairs_visited": LAST_PAIRS[0] if LAST_PAIRS else None,
                         "P_pairs_composited": LAST_PAIRS[1] if LAST_PAIRS else None}
     except LookupError as e:
@@ -477,14 +583,20 @@ def run_b200(args):
         cpu_baseline = {"value": None, "unit": "Mpix/s", "cores": 0, "kind": "port", "sample": f"failed: {e!r}"[:160]}
 
     line = {
+        "impl": "b200",
         "metric": metric_name(args.config), "value": value, "unit": "Mpix/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
         "scaling": "strong" if args.total_views else "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.config}: {N} gaussians SH{deg}, {W}x{H}, {V} view(s)/rank/step fwd+bwd"
-                               + (", gradients all-reduced in place (5 attribute tensors back to back; the store path reduces ONE flat 59N-float buffer) once per step" if world > 1 else ""),
-                   "N": N, "N_visible": n_vis, "M_isects": M, "views_per_rank": V, "view_streams": args.view_streams,
-                   "l2": "inputs larger than L2 (params 236 MB + keys/records > 126 MB); no explicit flush"},
+        "config": config_dict(args.config, V, n_vis, M, world, args.total_views),
+        "view_streams": args.view_streams,
+        # the same K steps with every view on ONE stream: the figure a caller that host-syncs between views can reach
+        "value_one_stream": (pix_per_step / (ms_one / args.steps / 1e3) / 1e6) if ms_one else value,
+        "ms_per_step_one_stream": (ms_one / args.steps) if ms_one else ms_dev / args.steps,
+        "reference_trainer_it_per_s": (ref_trainer or {}).get("it_per_s"),
+        "reference_trainer": ref_trainer,
+        "multi_gpu": multi_gpu,
+        "oracle_pin": gsplat_probe(),
         "e2e": {"value": e2e_val, "unit": "Mpix/s", "h2d_bytes_per_step": V * (W * H * 3 * 4 + 64), "d2h_bytes_per_step": 4,
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches,
@@ -521,6 +633,8 @@ def main():
     ap.add_argument("--views-per-rank", type=int, default=4)
     ap.add_argument("--view-streams", type=int, default=2,
                     help="CUDA streams the views of a step alternate over (ViewStreams); 1 = one stream")
+    ap.add_argument("--no-reference-trainer", action="store_true",
+                    help="skip the leg that times the reference's unmodified _training_step on B200Backend")
     ap.add_argument("--total-views", type=int, default=0,
                     help="fixed number of views per step split over the ranks (strong scaling, config B: 64); "
                          "default 0 = --views-per-rank views on every rank (weak scaling)")

@@ -214,3 +214,54 @@ def tensor_views(cams: torch.Tensor, images: List[torch.Tensor], K: torch.Tensor
     """What ``_to_tensor_view`` (trainer.py:270-281) builds per frame."""
     return [{"image": img.to(device=device, dtype=torch.float32), "pose": vm.to(device=device, dtype=torch.float32),
              "K": K.to(device=device, dtype=torch.float32), "width": W, "height": H} for vm, img in zip(cams, images)]
+
+
+# ------------------------------------------------------------------------------------------------------------
+# torch 2.11 CUDA avg_pool2d backward on the permuted views the reference's SSIM passes (trainer.py:487-490)
+# ------------------------------------------------------------------------------------------------------------
+def avgpool_permuted_backward_deviation(H: int = 90, W: int = 160) -> Dict[str, float]:
+    """L2-relative deviation of d(mean(avg_pool2d(x_chw)))-style SSIM gradients on CUDA from the CPU result, for the
+    reference's permuted [H,W,3] -> [1,3,H,W] views and for contiguous copies of them (profiles/avgpool_probe.py)."""
+    import torch.nn.functional as F
+
+    def ssim(a, b):
+        C1, C2 = 0.01 ** 2, 0.03 ** 2
+        mu1, mu2 = F.avg_pool2d(a, 3, 1, padding=1), F.avg_pool2d(b, 3, 1, padding=1)
+        s1 = F.avg_pool2d(a * a, 3, 1, padding=1) - mu1.pow(2)
+        s2 = F.avg_pool2d(b * b, 3, 1, padding=1) - mu2.pow(2)
+        s12 = F.avg_pool2d(a * b, 3, 1, padding=1) - mu1 * mu2
+        return (((2 * mu1 * mu2 + C1) * (2 * s12 + C2)) / ((mu1.pow(2) + mu2.pow(2) + C1) * (s1 + s2 + C2))).mean()
+
+    def grad(x, gt, dev, contiguous):
+        x = x.to(dev).double().requires_grad_(True)
+        a, b = x.permute(2, 0, 1).unsqueeze(0), gt.to(dev).double().permute(2, 0, 1).unsqueeze(0)
+        if contiguous:
+            a, b = a.contiguous(), b.contiguous()
+        ssim(a, b).backward()
+        return x.grad.cpu()
+
+    gen = torch.Generator().manual_seed(H)
+    x, gt = torch.rand(H, W, 3, generator=gen), torch.rand(H, W, 3, generator=gen)
+    ref = grad(x, gt, "cpu", False)
+    out = {}
+    for name, contiguous in (("permuted", False), ("contiguous", True)):
+        g = grad(x, gt, "cuda", contiguous)
+        out[name] = ((g - ref).norm() / ref.norm()).item()
+    return out
+
+
+@contextlib.contextmanager
+def contiguous_avg_pool2d():
+    """`torch.nn.functional.avg_pool2d` on a contiguous copy of its input for the duration of the block — the
+    reference's loss code is untouched; only torch's own CUDA backward defect on channels-last views is bypassed."""
+    import torch.nn.functional as F
+    orig = F.avg_pool2d
+
+    def fixed(x, *a, **k):
+        return orig(x.contiguous(), *a, **k)
+
+    F.avg_pool2d = fixed
+    try:
+        yield
+    finally:
+        F.avg_pool2d = orig

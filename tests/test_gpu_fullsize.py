@@ -1,5 +1,6 @@
-"""Full-size GPU parity (BASELINE.json configs[1] = config A: 1 M Gaussians SH3, 1920x1080) and the committed
-golden fixture.
+"""Full-size GPU parity at BASELINE.json's own sizes — configs[1] = A (1 M Gaussians SH3, 1920x1080; also with a posed
+camera and asymmetric intrinsics), configs[2] = B (3 M, three of the 64 circle cameras), configs[3] = C (6 M, 3840x2160)
+— and the committed golden fixture.
 
 At this size the PyTorch oracle is too slow, so the checker is the C/OpenMP port of the same spec
 (oracle/cpu_splat.c, validated against the PyTorch oracle and the golden fixture in tests/test_oracle_cpu.py),
@@ -107,7 +108,8 @@ def test_full_size_binning_bit_exact_against_c_port(pkg, oracle, name):
 @pytest.mark.parametrize("name", list(FULL))
 def test_full_size_render_and_gradients_match_c_port(pkg, oracle, name):
     """Image and parameter gradients at full size against the C port (fp32 like the GPU, so BOTH sides round):
-    image max-abs <= 1e-4 except on <= 0.5 % threshold-tied pixels, themselves capped at 0.05; gradients per Gaussian."""
+    image max-abs <= 1e-4 except on <= 0.01 % threshold-tied pixels (measured 5e-6 .. 1e-5 of the pixels), themselves
+    capped at 0.01 (measured <= 3.3e-3: one faint Gaussian's contribution); gradients per Gaussian (parity_util)."""
     from oracle import cpu_port
     cpu_port.set_threads(os.cpu_count() or 1)
     sc, act, cfg = _full_scene(oracle, name)
@@ -120,8 +122,8 @@ def test_full_size_render_and_gradients_match_c_port(pkg, oracle, name):
     mism = (meta["radii"][0].cpu() != ref["fw"]["radii"]).any(-1).float().mean().item()
     print(f"{name}: M gpu {meta['flatten_ids'].numel()} / cpu {ref['M']}; radii mismatch fraction {mism:.2e}")
     assert mism <= 1e-4, mism
-    image_close(r, ref["render"], None, max_marginal=5e-3, what=f"{name}/render")
-    image_close(al, ref["alpha"], None, max_marginal=5e-3, what=f"{name}/alpha")
+    image_close(r, ref["render"], None, max_marginal=1e-4, cap=0.01, what=f"{name}/render")
+    image_close(al, ref["alpha"], None, max_marginal=1e-4, cap=0.01, what=f"{name}/alpha")
     for k, g in leaves.items():
         grad_rows(g.grad, ref["grads"][k].reshape(g.shape), f"{k}/{name}")
 
@@ -214,7 +216,7 @@ def test_more_than_65536_tiles_takes_the_64bit_key_path(pkg, oracle):
     if torch.equal(meta["radii"][0].cpu(), ref["fw"]["radii"]):  # same projection bits -> binning must be identical
         assert torch.equal(meta["flatten_ids"].cpu(), ref["fw"]["flatten_ids"])
         assert torch.equal(meta["isect_offsets"][0].cpu(), ref["fw"]["isect_offsets"])
-    image_close(r, ref["render"], None, max_marginal=5e-3, what="69632-tiles/render")
+    image_close(r, ref["render"], None, max_marginal=1e-4, cap=0.01, what="69632-tiles/render")
     for k, g in leaves.items():
         grad_rows(g.grad, ref["grads"][k].reshape(g.shape), f"{k}/69632-tiles")
 

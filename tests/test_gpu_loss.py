@@ -95,3 +95,19 @@ def test_loss_drives_the_rasterizer(pkg, oracle):
     for k in grads[0]:
         rel = ((grads[0][k] - grads[1][k]).norm() / grads[1][k].norm()).item()
         assert rel <= 1e-3, (k, rel)
+
+
+def test_torch_avg_pool2d_backward_on_the_references_permuted_views():
+    """DESIGN.md §7 / VERDICT r1 item 3c.  The reference computes SSIM on `x.permute(2,0,1).unsqueeze(0)` — a channels-last
+    VIEW of the [H,W,3] render (src/training/trainer.py:487-490).  On this image (torch 2.11.0+cu128) the CUDA backward of
+    `avg_pool2d` for such inputs returns a gradient that differs from torch's own CPU result and from its CUDA result on a
+    contiguous copy by 57-73 % (L2-relative; forward values agree to rounding) — measured by profiles/avgpool_probe.py on
+    the B200 box.  The fused loss kernel (loss.cu) follows the CPU / contiguous result, i.e. it deliberately does NOT
+    reproduce that defect.  This test pins both facts: the contiguous formulation is the consistent one, and the
+    deviation of the permuted one is either the known defect (> 10 %) or gone (a fixed torch) — never a small drift."""
+    from dropin_harness import avgpool_permuted_backward_deviation
+    for H, W in ((16, 32), (90, 160)):
+        dev = avgpool_permuted_backward_deviation(H, W)
+        print(f"{H}x{W}: permuted {dev['permuted']:.3e}  contiguous {dev['contiguous']:.3e}")
+        assert dev["contiguous"] <= 1e-9
+        assert dev["permuted"] <= 1e-9 or dev["permuted"] >= 0.1
