@@ -41,6 +41,10 @@ SIGNATURES = {
     "b200_bin_emit_sorted": (_i, [_p, _p, _p, _p, _p, _l, _i, _i, _l, _p, _p, _p]),
     "b200_tile_ranges_k16": (_i, [_p, _l, _i, _p, _p]),
     "b200_isect_ids": (_i, [_p, _p, _p, _l, _p, _p]),
+    "b200_bin_coarse_supported": (_i, [_i, _i]),
+    "b200_bin_coarse_scratch_bytes": (_z, [_l, _l]),
+    "b200_bin_coarse": (_i, [_p, _p, _p, _p, _l, _i, _i, _p, _l, _p, _p, _p, _p, _p, _p, _z, _p]),
+    "b200_isect_ids_from_offsets": (_i, [_p, _p, _i, _p, _l, _p, _p]),
     "b200_bin_scan": (_i, [_p, _l, _p, _p, _p]),
     "b200_bin_emit": (_i, [_p, _p, _p, _p, _l, _i, _i, _l, _p, _p, _p, _p]),
     "b200_sort_scratch_bytes": (_z, [_l]),
@@ -53,6 +57,7 @@ SIGNATURES = {
     "b200_project_sh_bwd_raw": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _i, _p]),
     "b200_l1_ssim_fwd_bwd": (_i, [_p, _p, _i, _i, C.c_float, C.c_float, _p, _p, _p]),
     "b200_adam_step": (_i, [_p, _p, _p, _p, _l, _p, _i, _i, C.c_float, C.c_float, C.c_float, _p]),
+    "b200_adam_step_stats": (_i, [_p, _p, _p, _p, _l, _p, _i, _i, C.c_float, C.c_float, C.c_float, _p, _l, _p, _p, _p]),
     "b200_store_gather": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _l, _p]),
     "b200_densify_stats": (_i, [_p, _l, _p, _p, _p]),
 }

@@ -140,15 +140,19 @@ __global__ void __launch_bounds__(RS_THREADS)
 rs_onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                    KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out, uint32_t n, int shift,
                    uint32_t dmask, const uint32_t* __restrict__ digit_base, volatile uint32_t* __restrict__ status,
-                   uint32_t* __restrict__ ticket) {
+                   uint32_t* __restrict__ ticket, const uint32_t* __restrict__ n_dev) {
     extern __shared__ __align__(16) unsigned char rs_smem_raw[];
     RsSmem<KeyT>& S = *reinterpret_cast<RsSmem<KeyT>*>(rs_smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
 
+    // n_dev: the element count lives on the device (the coarse binning path sizes its launch by an upper bound known to
+    // the host and lets the surplus CTAs leave here); tickets are handed out in order, so the leavers are the last ones
+    if (n_dev != nullptr) n = __ldg(n_dev);
     if (tid == 0) S.tile = atomicAdd(ticket, 1u);
     for (int i = tid; i < RS_WARPS * RS_RADIX; i += RS_THREADS) (&S.warp_hist[0][0])[i] = 0;
     __syncthreads();
     const uint32_t tile = S.tile;
+    if ((uint64_t)tile * RS_TILE >= n) return;
     const uint32_t tile_base = tile * RS_TILE;
     const uint32_t n_valid = min((uint32_t)RS_TILE, n - tile_base);
     const bool full = n_valid == RS_TILE;
@@ -285,19 +289,26 @@ rs_onesweep_kernel(const KeyT* __restrict__ keys_in, const uint32_t* __restrict_
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// begin_bit: lowest key bit that takes part (bits below ride along as payload).  n_dev: device-side element count
+// <= M (M then only sizes the launch and the scratch).  prepared_base: exclusive digit offsets of every pass supplied
+// by the caller (no histogram pass).
 template <typename KeyT>
 int sort_pairs_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_t* vals_b, int64_t M, int end_bit,
                     void* scratch, size_t scratch_bytes, int* result_in_b_host, void* stream, const char* what,
-                    const uint32_t* prepared_base = nullptr) {
-    if (!(M >= 0 && end_bit > 0 && end_bit <= (int)(8 * sizeof(KeyT)))) {
+                    const uint32_t* prepared_base = nullptr, int begin_bit = 0, const uint32_t* n_dev = nullptr) {
+    if (!(M >= 0 && begin_bit >= 0 && end_bit > begin_bit && end_bit <= (int)(8 * sizeof(KeyT)))) {
         b200_set_error("%s: bad sizes", what);
+        return B200_EARG;
+    }
+    if (n_dev != nullptr && prepared_base == nullptr) {
+        b200_set_error("%s: a device-side count needs prepared digit bases", what);
         return B200_EARG;
     }
     if (M >= ((int64_t)1 << 30)) {
         b200_set_error("%s: M >= 2^30 not supported", what);
         return B200_EARG;
     }
-    const int npasses = (end_bit + RS_BITS - 1) / RS_BITS;
+    const int npasses = (end_bit - begin_bit + RS_BITS - 1) / RS_BITS;
     if (result_in_b_host) *result_in_b_host = (M > 0) ? (npasses & 1) : 0;
     if (M == 0) return B200_OK;
     if (!(keys_a && vals_a && keys_b && vals_b && scratch)) {
@@ -334,17 +345,21 @@ int sort_pairs_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_t* vals
     int hist_blocks = (int)min((int64_t)hb, (M + 255) / 256);
     const int hist_threads = (npasses <= 4) ? 256 : 128;  // warps * npasses <= RS_HIST_ROWS
     if (prepared_base == nullptr) {
-        rs_hist_kernel<KeyT><<<hist_blocks, hist_threads, 0, st>>>(keys_a, M, npasses, end_bit, hist);
+        rs_hist_kernel<KeyT><<<hist_blocks, hist_threads, 0, st>>>(keys_a, M, npasses, end_bit, hist);  // (begin_bit == 0 here)
         rs_scan_kernel<<<npasses, RS_RADIX, 0, st>>>(hist);
     }
     const uint32_t* bases = prepared_base ? prepared_base : hist;
     KeyT* kin = keys_a; uint32_t* vin = vals_a; KeyT* kout = keys_b; uint32_t* vout = vals_b;
     const size_t smem = sizeof(RsSmem<KeyT>) + pad;
+    if (prepared_base == nullptr && begin_bit != 0) {
+        b200_set_error("%s: begin_bit needs prepared digit bases", what);
+        return B200_EARG;
+    }
     for (int p = 0; p < npasses; ++p) {
-        int shift = p * RS_BITS;
+        int shift = begin_bit + p * RS_BITS;
         int bits = (end_bit - shift) < RS_BITS ? (end_bit - shift) : RS_BITS;
 #define RS_LAUNCH(B) rs_onesweep_kernel<KeyT, B><<<(unsigned)ntiles, RS_THREADS, smem, st>>>( \
-        kin, vin, kout, vout, (uint32_t)M, shift, (1u << bits) - 1u, bases + p * RS_RADIX, status + (size_t)p * ntiles * RS_RADIX, tickets + p)
+        kin, vin, kout, vout, (uint32_t)M, shift, (1u << bits) - 1u, bases + p * RS_RADIX, status + (size_t)p * ntiles * RS_RADIX, tickets + p, n_dev)
         // digits narrower than 5 bits run the 5-bit kernel (the upper ballots see zeros): same result
         if (bits >= 8) RS_LAUNCH(8); else if (bits == 7) RS_LAUNCH(7); else if (bits == 6) RS_LAUNCH(6); else RS_LAUNCH(5);
 #undef RS_LAUNCH
@@ -355,6 +370,15 @@ int sort_pairs_impl(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_t* vals
 }
 
 }  // namespace
+
+// Used by the coarse binning path (binning.cu): (supertile << 16 | coverage mask) keys sorted on bits [16, end_bit) with
+// caller-supplied digit bases and a device-side element count.
+int b200_sort_pairs_coarse(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b, int64_t cap, int end_bit,
+                           const uint32_t* digit_base, const uint32_t* n_dev, void* scratch, size_t scratch_bytes,
+                           int* result_in_b_host, void* stream) {
+    return sort_pairs_impl<uint32_t>(keys_a, vals_a, keys_b, vals_b, cap, end_bit, scratch, scratch_bytes, result_in_b_host,
+                                     stream, "b200_bin_coarse(sort)", digit_base, 16, n_dev);
+}
 
 extern "C" size_t b200_sort_scratch_bytes(int64_t M) {
     if (M < 0) M = 0;

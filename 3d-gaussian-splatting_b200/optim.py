@@ -52,7 +52,10 @@ class StoreAdam:
         return (C.c_double * len(flat))(*flat), len(rows)
 
     @torch.no_grad()
-    def step(self) -> None:
+    def step(self, densify_stats: bool = False) -> None:
+        """One Adam step over the flat store.  densify_stats=True also takes the reference's densification statistic
+        (trainer.py:786-791: ``accum += ||xyz.grad||``, ``count += 1``, right after ``optimizer.step()``) in the same
+        kernel — the position gradient is already being streamed — instead of a separate ``densify_stats`` launch."""
         st = self.store
         # the moments are laid out like `store.flat`: a store that was re-allocated without this optimiser
         # (densify_and_prune(optimizer=None) — the reference's signature default) would be stepped out of bounds or with
@@ -63,9 +66,17 @@ class StoreAdam:
         self.t += 1
         segs, n_seg = self._segments()
         with torch.cuda.device(st.flat.device):
-            check(lib.b200_adam_step(st.flat.data_ptr(), st.flat_grad.data_ptr(), self.exp_avg.data_ptr(),
-                                     self.exp_avg_sq.data_ptr(), st.flat.numel(), segs, n_seg, self.t, self.betas[0],
-                                     self.betas[1], self.eps, torch.cuda.current_stream().cuda_stream), "b200_adam_step")
+            g = st.flat_grad
+            if densify_stats:
+                check(lib.b200_adam_step_stats(st.flat.data_ptr(), g.data_ptr(), self.exp_avg.data_ptr(),
+                                               self.exp_avg_sq.data_ptr(), st.flat.numel(), segs, n_seg, self.t, self.betas[0],
+                                               self.betas[1], self.eps, g.data_ptr() + 4 * st._offsets["xyz"], len(st),
+                                               st.xyz_gradient_accum.data_ptr(), st.xyz_gradient_count.data_ptr(),
+                                               torch.cuda.current_stream().cuda_stream), "b200_adam_step_stats")
+            else:
+                check(lib.b200_adam_step(st.flat.data_ptr(), g.data_ptr(), self.exp_avg.data_ptr(),
+                                         self.exp_avg_sq.data_ptr(), st.flat.numel(), segs, n_seg, self.t, self.betas[0],
+                                         self.betas[1], self.eps, torch.cuda.current_stream().cuda_stream), "b200_adam_step")
 
     def zero_grad(self, set_to_none: bool = False, lazy: bool = False) -> None:
         self.store.zero_grad(lazy=lazy)  # lazy: see GaussianStore.zero_grad

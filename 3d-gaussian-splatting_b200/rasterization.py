@@ -96,6 +96,19 @@ def _pinned_scalar(dev: torch.device) -> torch.Tensor:
     return t
 
 
+_SIDE_STREAMS = {}
+
+
+def _side_stream(dev: torch.device) -> torch.cuda.Stream:
+    """One helper stream per device for the single-CTA tile_prep kernel + the read-back of M: both depend only on the
+    projection and run UNDER the depth sort of the launching stream (forked and joined with events)."""
+    s = _SIDE_STREAMS.get(dev)
+    if s is None:
+        s = torch.cuda.Stream(device=dev)
+        _SIDE_STREAMS[dev] = s
+    return s
+
+
 def tile_n_bits(tile_w: int, tile_h: int) -> int:
     """gsplat's key width: floor(log2(n_tiles)) + 1 — one more bit than the largest tile id needs when
     n_tiles is a power of two (65 536 tiles -> 17)."""
@@ -122,6 +135,10 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
     ranges and digit histograms come from the corner-difference grid (b200_tile_prep).
     method "split-hist": the split path with a histogram pass and tile_ranges over the sorted keys instead
     (what "split" falls back to when the tile grid does not fit b200_tile_prep).
+    method "coarse" (the default whenever b200_bin_coarse_supported): depth sort over the Gaussians as in "split", then
+    TWO-LEVEL binning — (Gaussian, 4x4-tile supertile) pairs are emitted in depth order, sorted on the supertile id, and
+    expanded per supertile straight into the final per-tile lists (include/b200splat.h, b200_bin_coarse): the M
+    intersections are written once (4 B each) and never sorted.  Same flatten_ids / isect_offsets, bit for bit.
     """
     dev = means.device
     N = means.shape[0]
@@ -130,6 +147,14 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
     n_tiles = tile_w * tile_h
     if method == "auto":
         method = "split" if (n_tiles <= 65536 and not keep_unsorted) else "keys64"
+        if method == "split" and (tile_w + 1) * (tile_h + 1) <= int(lib.b200_tile_prep_max_cells()) \
+                and lib.b200_bin_coarse_supported(width, height):
+            method = "coarse"
+    coarse = method == "coarse"
+    if coarse:
+        if not lib.b200_bin_coarse_supported(width, height) or (tile_w + 1) * (tile_h + 1) > int(lib.b200_tile_prep_max_cells()):
+            raise ValueError("binning='coarse' needs a tile grid within b200_bin_coarse_supported / b200_tile_prep limits")
+        method = "split"  # same front half: depth keys, corner grid, tile_prep, depth sort
     st = _stream()
     if sh_degree is None:
         sh_coeffs, deg = 1, -1
@@ -192,15 +217,22 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
     if prep:
         digit_base = torch.empty(512, dtype=torch.int32, device=dev)
         total_prep = torch.empty(1, dtype=torch.int64, device=dev)
-        with _stage("tile_prep"):
-            check(lib.b200_tile_prep(_ptr(tile_grid), width, height, _ptr(offsets), _ptr(total_prep), _ptr(digit_base), st),
-                  "b200_tile_prep")
-        # M is known here, before the depth sort: start its read-back now and collect it after the depth-sort
-        # launches are queued, so the host never waits on an idle GPU
+        # tile_prep (one CTA: 2-D prefix sum of the corner grid -> per-tile ranges, M) and the read-back of M depend only
+        # on the projection: they go on a side stream and run under the depth sort.  The launching stream joins before it
+        # first needs the ranges; the host collects M after the depth-sort launches are queued, so it never waits on an
+        # idle GPU.
+        cur, side = torch.cuda.current_stream(dev), _side_stream(dev)
+        fork = torch.cuda.Event()
+        fork.record(cur)
+        side.wait_event(fork)
         m_host = _pinned_scalar(dev)
-        m_host.copy_(total_prep, non_blocking=True)
         m_ready = torch.cuda.Event()
-        m_ready.record()
+        with torch.cuda.stream(side):
+            with _stage("tile_prep"):
+                check(lib.b200_tile_prep(_ptr(tile_grid), width, height, _ptr(offsets), _ptr(total_prep), _ptr(digit_base),
+                                         side.cuda_stream), "b200_tile_prep")
+            m_host.copy_(total_prep, non_blocking=True)
+            m_ready.record(side)
     dkeys_b = torch.empty_like(dkeys_a)
     gids_b = torch.empty_like(gids_a)
     scratch_n = _sort_scratch(N, dev)
@@ -209,6 +241,30 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
                                       _ptr(scratch_n), scratch_n.numel(), C.byref(in_b), st), "b200_sort_pairs_k32",
               kernels=6 if N > 0 else 0)
     perm = gids_b if in_b.value else gids_a
+    if prep:
+        torch.cuda.current_stream(dev).wait_event(m_ready)  # join: ranges / digit bases are used from here on
+    if coarse:
+        m_ready.synchronize()  # the one host wait of the forward pass (sizes the intersection buffers)
+        M = int(m_host.item())
+        cap = max(M, 1)
+        ck = torch.empty(4, cap, dtype=torch.int32, device=dev)  # pair keys / ids, double-buffered (M' <= M used)
+        flat_ids = torch.empty(cap, dtype=torch.int32, device=dev)
+        sb = int(lib.b200_bin_coarse_scratch_bytes(N, M))
+        scratch_c = torch.empty(max(sb, 256), dtype=torch.uint8, device=dev)
+        with _stage("bin_coarse"):
+            check(lib.b200_bin_coarse(_ptr(splats), _ptr(radii), _ptr(tiles_per_gauss), _ptr(perm), N, width, height,
+                                      _ptr(offsets), M, _ptr(ck[0]), _ptr(ck[1]), _ptr(ck[2]), _ptr(ck[3]), _ptr(flat_ids),
+                                      _ptr(scratch_c), scratch_c.numel(), st), "b200_bin_coarse",
+                  kernels=(3 + (2 if n_tiles > 16 * 256 else 1)) if (N > 0 and M > 0) else 0)
+        out.update(M=M, flatten_ids=flat_ids[:M], isect_offsets=offsets.view(tile_h, tile_w), tile_keys=None)
+        if with_isect_ids:
+            ids = torch.empty(cap, dtype=torch.int64, device=dev)
+            check(lib.b200_isect_ids_from_offsets(_ptr(flat_ids), _ptr(offsets), n_tiles, _ptr(splats), M, _ptr(ids), st),
+                  "b200_isect_ids_from_offsets", kernels=1 if M > 0 else 0)
+            out["isect_ids"] = ids[:M]
+        else:
+            out["isect_ids"] = None
+        return out
     with _stage("bin_scan"):
         check(lib.b200_bin_count_sorted(_ptr(tiles_per_gauss), _ptr(perm), N, _ptr(block_sums), st),
               "b200_bin_count_sorted", kernels=1 if N > 0 else 0)

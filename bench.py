@@ -264,10 +264,8 @@ def run_b200(args):
     # drain phase of one view run under the long blend kernels of the other
     vstreams = pkg.ViewStreams(dev, args.view_streams, params_list)
 
-    _vi = view_index
-
-    def view_index(step, v):  # noqa: F811 — this rank's camera sequence
-        return _vi(step, v, V, rank, world)
+    def my_view(step, v):  # this rank's camera sequence
+        return view_index(step, v, V, rank, world)
 
     probe = {"on": False, "render": [], "reduce": []}  # CUDA events of the multi-GPU diagnostic pass (not the headline)
 
@@ -282,7 +280,7 @@ def run_b200(args):
         vstreams.begin()
         for v in range(V):
             with vstreams.view(v):
-                vp = {"world_view_transform": poses_dev[view_index(step, v)], "image_width": W, "image_height": H}
+                vp = {"world_view_transform": poses_dev[my_view(step, v)], "image_width": W, "image_height": H}
                 res = backend.render_with_depth(leaves, vp, bg_color=bg, render_mode="RGB", device="cuda", sh_degree=deg)
                 res["render"].backward(v_render)
         vstreams.join()
@@ -328,10 +326,10 @@ def run_b200(args):
                 if not e2e_state["primed"]:
                     for sl in range(2):
                         free_ev[sl].record(cur)
-                    upload(slot, view_index(step, v))
+                    upload(slot, my_view(step, v))
                     e2e_state["primed"] = True
                 nv, ns = (v + 1, step) if v + 1 < V else (0, step + 1)
-                upload(slot ^ 1, view_index(ns, nv))  # prefetch the next view while this one renders
+                upload(slot ^ 1, my_view(ns, nv))  # prefetch the next view while this one renders
                 cur.wait_event(ready_ev[slot])
                 vp = {"world_view_transform": pose_slot[slot], "image_width": W, "image_height": H}
                 res = backend.render_with_depth(leaves, vp, bg_color=bg, render_mode="RGB", device="cuda", sh_degree=deg)
@@ -356,7 +354,7 @@ def run_b200(args):
         vstreams.begin()
         for v in range(V):
             with vstreams.view(v):
-                vp = {"world_view_transform": poses_dev[view_index(step, v)], "image_width": W, "image_height": H}
+                vp = {"world_view_transform": poses_dev[my_view(step, v)], "image_width": W, "image_height": H}
                 res = store.render(K, vp, bg_color=bg, render_mode="RGB", sh_degree=deg)
                 res["render"].backward(v_render)
         vstreams.join()
@@ -383,10 +381,10 @@ def run_b200(args):
                 if not train_state["primed"]:
                     for sl in range(2):
                         free_ev[sl].record(cur)
-                    upload(slot, view_index(step, v))
+                    upload(slot, my_view(step, v))
                     train_state["primed"] = True
                 nv, ns = (v + 1, step) if v + 1 < V else (0, step + 1)
-                upload(slot ^ 1, view_index(ns, nv))
+                upload(slot ^ 1, my_view(ns, nv))
                 cur.wait_event(ready_ev[slot])
                 vp = {"world_view_transform": pose_slot[slot], "image_width": W, "image_height": H}
                 res = store.render(K, vp, bg_color=bg, render_mode="RGB", sh_degree=deg)
@@ -398,8 +396,7 @@ def run_b200(args):
         vstreams.join()
         if world > 1:
             pkg.allreduce_flat(store.flat_grad, 1.0 / world)
-        adam.step()
-        pkg.densify_stats(store.xyz_gradient_accum, store.xyz_gradient_count, store.xyz.grad)
+        adam.step(densify_stats=True)  # K10 rides in the optimiser pass (adam.cu)
         return float(torch.stack(losses).sum().item())
 
     def timed(fn, steps, warmup, timer=None):
@@ -501,7 +498,7 @@ def run_b200(args):
             tviews = dh.tensor_views([cams[i] for i in range(64)], [gts[i & 1] for i in range(64)], sc["K"], W, H, "cuda")
 
             def step_ref(step):
-                trainer._training_step(model, rast, [tviews[view_index(step, v)] for v in range(V)], opt)
+                trainer._training_step(model, rast, [tviews[my_view(step, v)] for v in range(V)], opt)
 
             ms_ref, ref_launches = timed(step_ref, args.steps, 3)
             ref_trainer = {"it_per_s": 1e3 / (ms_ref / args.steps), "ms_per_step": ms_ref / args.steps,
@@ -532,6 +529,9 @@ def run_b200(args):
     alg = {
         "project_sh_fwd": n_vis * 280 + (N - n_vis) * 52,
         "bin_emit": M * 12 + N * 16,
+        # two-level binning (emit + pair sort + expansion in one C call): the reference formulation's emit (12 B) + sort
+        # (24 B compulsory) per intersection, SURVEY §8d
+        "bin_coarse": M * 36 + N * 16,
         "sort_pairs": M * 24,
         "tile_ranges": M * 8,
         "tile_prep": ((W + 15) // 16 + 1) * ((H + 15) // 16 + 1) * 4 + ((W + 15) // 16) * ((H + 15) // 16) * 4,

@@ -131,6 +131,29 @@ int b200_bin_count_sorted(const int32_t* tiles_per_gauss, const int32_t* perm, i
 int b200_bin_emit_sorted(const float* splats, const int32_t* radii, const int32_t* tiles_per_gauss,
                          const int32_t* perm, const int64_t* block_offsets, int64_t N, int width,
                          int height, int64_t M, uint16_t* tile_keys, int32_t* flatten_ids, void* stream);
+/* ---- two-level binning (default fast path) ------------------------------------------------------------------------
+ * Same result as gsplat isect_tiles(sort=True) + isect_offset_encode (gsplat_backend.py:168-182) — flatten_ids and
+ * isect_offsets bit for bit — without sorting the M intersections.  Inputs: projection outputs, `perm` = Gaussian ids
+ * in depth order (b200_sort_pairs_k32 of the depth keys), isect_offsets and M from b200_tile_prep.
+ *   1. (Gaussian, supertile) pairs, supertile = 4x4 tiles, are emitted in depth order as
+ *      (supertile << 16 | 16-bit mask of the covered tiles, id); output offsets by a decoupled look-back scan inside the
+ *      kernel, per-supertile counts in CTA-private histograms (M' pairs, M' ~ M/3..M/5, M' <= M);
+ *   2. one small kernel turns the counts into supertile ranges and radix digit bases;
+ *   3. the pairs are sorted stably on the supertile bits (one or two 8-bit onesweep passes over M', count on the device);
+ *   4. one CTA per supertile, one warp per tile, streams the supertile's list once and compacts the ids covering its
+ *      tile into flatten_ids[isect_offsets[tile] ...] in list order (= depth order, ties by ascending Gaussian index).
+ * keys_a/vals_a/keys_b/vals_b: M uint32 each (only M' used); scratch: b200_bin_coarse_scratch_bytes(N, M) bytes.
+ * Needs b200_bin_coarse_supported(width, height): <= 65 536 tiles and <= 4096 supertiles. */
+int b200_bin_coarse_supported(int width, int height);
+size_t b200_bin_coarse_scratch_bytes(int64_t N, int64_t M_cap);
+int b200_bin_coarse(const float* splats, const int32_t* radii, const int32_t* tiles_per_gauss, const int32_t* perm,
+                    int64_t N, int width, int height, const int32_t* isect_offsets, int64_t M,
+                    uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b,
+                    int32_t* flatten_ids, void* scratch, size_t scratch_bytes, void* stream);
+/* gsplat's sorted 64-bit isect_ids rebuilt from (flatten_ids, isect_offsets) for callers that ask (parity tests, meta). */
+int b200_isect_ids_from_offsets(const int32_t* flatten_ids, const int32_t* isect_offsets, int n_tiles,
+                                const float* splats, int64_t M, int64_t* isect_ids, void* stream);
+
 /* Per-tile ranges and radix digit bases WITHOUT a pass over the intersections: the 2-D prefix sum of
  * tile_grid (written by b200_project_sh_fwd) is the intersection count of every tile, so
  *   offsets[n_tiles]  = row-major exclusive scan          (== b200_tile_ranges_k16 of the sorted keys),
@@ -226,6 +249,13 @@ int b200_l1_ssim_fwd_bwd(const float* render, const float* gt, int width, int he
 int b200_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n_floats,
                    const double* seg_host, int n_seg, int step, float beta1, float beta2, float eps,
                    void* stream);
+/* Same pass with stage 5 riding along (trainer.py:786-791 takes the statistic right after optimizer.step(), from the
+ * same, untouched xyz.grad): accum[n_gauss,3] += ||xyz_grad||_2, count[n_gauss] += 1 for every Gaussian, by the first
+ * n_gauss threads of the launch — replaces a separate b200_densify_stats launch.  A segment's `begin` may be negative
+ * (a rank stepping only a slice of the flat buffer passes offset pointers and shifted segments). */
+int b200_adam_step_stats(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n_floats,
+                         const double* seg_host, int n_seg, int step, float beta1, float beta2, float eps,
+                         const float* xyz_grad, int64_t n_gauss, float* accum, float* count, void* stream);
 
 /* ---- f2: population change of the flat store in one gather -----------------------
  * Data movement of gaussian_model.py:110-366 (clone / split / prune with the Adam moments spliced,

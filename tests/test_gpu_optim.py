@@ -75,3 +75,48 @@ def test_scale_ceiling_is_the_reference_clamp(pkg, oracle):
     st.scaling.grad.fill_(-1.0)
     opt.step()
     assert st.scaling.max().item() > ceiling
+
+
+@pytest.mark.parametrize("N", [1, 1000, 100_003])
+def test_adam_with_fused_densify_statistic(pkg, oracle, N):
+    """`StoreAdam.step(densify_stats=True)`: the stage-5 statistic (trainer.py:786-791) taken inside the optimiser pass
+    equals `optimizer.step()` followed by the reference's three torch ops, bit for bit on the parameters."""
+    sc = oracle.synthetic_scene(N, 64, 48, seed=23)
+    mk = lambda: pkg.GaussianStore.from_tensors(sc["xyz"].to(DEV), sc["features_dc"].to(DEV), sc["features_rest"].to(DEV),  # noqa: E731
+                                                sc["scaling"].to(DEV), sc["rotation"].to(DEV), sc["opacity"].to(DEV))
+    a, b = mk(), mk()
+    oa, ob = pkg.StoreAdam(a, LRS), pkg.StoreAdam(b, LRS)
+    gen = torch.Generator().manual_seed(8)
+    for it in range(3):
+        g = torch.randn(a.flat.numel(), generator=gen).to(DEV)
+        for st in (a, b):
+            st.zero_grad()
+            st.flat_grad.copy_(g)
+        oa.step(densify_stats=True)
+        ob.step()
+        with torch.no_grad():  # the reference's ops
+            b.xyz_gradient_accum += torch.norm(b.xyz.grad, dim=-1, keepdim=True)
+            b.xyz_gradient_count += 1
+        assert torch.equal(a.flat, b.flat)
+        torch.testing.assert_close(a.xyz_gradient_accum, b.xyz_gradient_accum, rtol=1e-6, atol=1e-7)
+        assert torch.equal(a.xyz_gradient_count, b.xyz_gradient_count) and float(a.xyz_gradient_count.min()) == it + 1
+
+
+def test_store_adam_refuses_a_store_reallocated_behind_its_back(pkg, oracle):
+    """`densify_and_prune(optimizer=None)` (the reference's signature default) re-lays the flat buffer; stepping
+    the old moments would read out of bounds.  torch's Adam raises in that situation; so must StoreAdam."""
+    sc = oracle.synthetic_scene(5000, 64, 48, seed=24)
+    st = pkg.GaussianStore.from_tensors(sc["xyz"].to(DEV), sc["features_dc"].to(DEV), sc["features_rest"].to(DEV),
+                                        sc["scaling"].to(DEV), sc["rotation"].to(DEV), sc["opacity"].to(DEV))
+    opt = pkg.StoreAdam(st, LRS)
+    st.xyz_gradient_accum.fill_(1.0)
+    st.xyz_gradient_count.fill_(1.0)
+    stats = st.densify_and_prune(1e-4, 0.05, 0.2, None, optimizer=None)
+    assert stats["n_after"] != stats["n_before"]
+    with pytest.raises(RuntimeError, match="re-allocated"):
+        opt.step()
+    opt2 = pkg.StoreAdam(st, LRS)
+    st.zero_grad()
+    opt2.step()
+    stats = st.densify_and_prune(1e-4, 0.05, 0.2, None, optimizer=opt2)  # spliced: keeps stepping
+    opt2.step()

@@ -147,6 +147,17 @@ def test_split_key_binning_bit_exact(pkg, oracle, N, W, H, cam):
     assert torch.equal(b["isect_ids"].cpu(), ids_s)
     assert torch.equal(b["flatten_ids"].cpu(), flat_s)
     assert torch.equal(b["isect_offsets"].cpu(), offs)
+    # the default fast path — two-level binning: (Gaussian, supertile) pairs sorted, expanded per supertile — gives the
+    # same lists without ever sorting the M intersections
+    if pkg._lib.lib.b200_bin_coarse_supported(W, H) and ((W + 15) // 16 + 1) * ((H + 15) // 16 + 1) <= pkg._lib.lib.b200_tile_prep_max_cells():
+        bc = pkg.project_and_bin(a["means3D"], a["rotations"], a["scales"], a["opacities"].squeeze(-1).contiguous(),
+                                 a["shs"], 3, cam, W, H, method="coarse", with_isect_ids=True)
+        assert bc["M"] == b["M"]
+        assert torch.equal(bc["flatten_ids"].cpu(), flat_s) and torch.equal(bc["isect_offsets"].cpu(), offs)
+        assert torch.equal(bc["isect_ids"].cpu(), ids_s)
+        ba = pkg.project_and_bin(a["means3D"], a["rotations"], a["scales"], a["opacities"].squeeze(-1).contiguous(),
+                                 a["shs"], 3, cam, W, H)  # "auto" resolves to it
+        assert torch.equal(ba["flatten_ids"], bc["flatten_ids"]) and ba["tile_keys"] is None
     # and the literal 64-bit path agrees with it
     b64 = pkg.project_and_bin(a["means3D"], a["rotations"], a["scales"], a["opacities"].squeeze(-1).contiguous(),
                               a["shs"], 3, cam, W, H, method="keys64")
@@ -172,6 +183,40 @@ def test_split_key_ties_keep_gaussian_order(pkg, oracle):
     ob = oracle.bin_tiles(sp[:, 0:2], radii, sp[:, 9], W, H)
     ids_s, flat_s, offs = oracle.sort_and_ranges(ob["isect_ids"], ob["flatten_ids"], ob["tile_w"], ob["tile_h"])
     assert torch.equal(b["flatten_ids"].cpu(), flat_s) and torch.equal(b["isect_ids"].cpu(), ids_s)
+    bc = pkg.project_and_bin(a["means3D"], a["rotations"], a["scales"], a["opacities"].squeeze(-1).contiguous(),
+                             a["shs"], 3, cam, W, H, method="coarse", with_isect_ids=True)
+    assert torch.equal(bc["flatten_ids"].cpu(), flat_s) and torch.equal(bc["isect_ids"].cpu(), ids_s)
+
+
+@pytest.mark.parametrize("W,H", [(64, 64), (200, 120), (1000, 40), (17, 300), (1920, 1080)])
+def test_two_level_binning_edge_cases(pkg, oracle, W, H):
+    """Screen-filling Gaussians (every supertile, full masks), image sizes that are not multiples of the 64-px supertile,
+    single-tile Gaussians, identical depths, one Gaussian, nothing visible — against the stable sort of the 64-bit keys."""
+    K = torch.tensor([[0.7 * max(W, H), 0, W / 2], [0, 0.7 * max(W, H), H / 2], [0, 0, 1]])
+    g = torch.Generator().manual_seed(W * 7 + H)
+    n = 600
+    means = torch.cat([torch.tensor([[0.0, 0.0, 3.0], [0.1, -0.1, 3.0], [0.0, 0.0, 0.5]]),            # two at the same depth, one huge
+                       torch.stack([(torch.rand(n, generator=g) - 0.5) * 4, (torch.rand(n, generator=g) - 0.5) * 3,
+                                    1.0 + 5 * torch.rand(n, generator=g)], -1)])
+    scales = torch.cat([torch.tensor([[2.0, 2.0, 0.1], [0.5, 0.5, 0.5], [0.3, 0.3, 0.3]]), 0.002 + 0.05 * torch.rand(n, 3, generator=g)])
+    N = means.shape[0]
+    quats = torch.nn.functional.normalize(torch.randn(N, 4, generator=g), dim=-1)
+    opac = torch.cat([torch.tensor([0.9, 0.9, 0.9]), torch.rand(n, generator=g)])
+    shs = 0.1 * torch.randn(N, 16, 3, generator=g)
+    cam = pkg.make_cam(torch.eye(4), K, W, H)
+    dev_args = [t.to(DEV).contiguous() for t in (means, quats, scales, opac, shs)]
+    for sel in (slice(None), slice(0, 1), slice(3, 4)):
+        args = [t[sel].contiguous() for t in dev_args]
+        ref = pkg.project_and_bin(*args, 3, cam, W, H, method="keys64")
+        got = pkg.project_and_bin(*args, 3, cam, W, H, method="coarse", with_isect_ids=True)
+        assert got["M"] == ref["M"]
+        assert torch.equal(got["flatten_ids"], ref["flatten_ids"]) and torch.equal(got["isect_offsets"], ref["isect_offsets"])
+        assert torch.equal(got["isect_ids"], ref["isect_ids"])
+    # nothing visible: M = 0
+    far = dev_args[0].clone()
+    far[:, 2] = -1.0
+    got = pkg.project_and_bin(far, *dev_args[1:], 3, cam, W, H, method="coarse")
+    assert got["M"] == 0 and got["flatten_ids"].numel() == 0 and int(got["isect_offsets"].abs().sum()) == 0
 
 
 @pytest.mark.parametrize("N,W,H", [(3000, 160, 96), (50000, 640, 360), (20000, 1920, 1080)])
