@@ -66,7 +66,7 @@ class B200Backend:
         result = {"render": rendered[..., :3], "alpha": alphas.squeeze(0), "depth": rendered[..., 3]}
         result["means2d"] = meta["means2d"][0]
         result["radii"] = meta["radii"][0]
-        result["visibility_filter"] = result["radii"] > 0
+        result["visibility_filter"] = meta["visibility_filter"][0]  # = radii > 0, from the projection kernel
         result["tiles_touched"] = meta["tiles_per_gauss"][0]  # key the reference probes
         return result
 
@@ -112,5 +112,5 @@ class B200Backend:
             result["means2d"] = meta["means2d"][0]
         if "radii" in meta:
             result["radii"] = meta["radii"][0]
-            result["visibility_filter"] = result["radii"] > 0
+            result["visibility_filter"] = meta["visibility_filter"][0]  # = radii > 0, from the projection kernel
         return result

@@ -37,7 +37,7 @@ Cam b200_make_cam(const float* c, int W, int H) {
     return cam;
 }
 
-extern "C" int b200_version(void) { return 100; }
+extern "C" int b200_version(void) { return 200; }  // round 2: coarse binning, auxiliary projection outputs
 extern "C" const char* b200_last_error(void) { return g_err; }
 
 // accum[N,3] += ||g||_2 ; count[N] += 1   (reference src/training/trainer.py:786-791)

@@ -251,7 +251,8 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
                       int32_t* __restrict__ radii, float* __restrict__ splats,
                       int32_t* __restrict__ tiles_per_gauss, int64_t* __restrict__ block_sums,
                       uint32_t* __restrict__ depth_keys, int32_t* __restrict__ gauss_ids,
-                      int32_t* __restrict__ tile_grid, const Cam* __restrict__ cam_g) {
+                      int32_t* __restrict__ tile_grid, const Cam* __restrict__ cam_g,
+                      uchar2* __restrict__ visibility, float4* __restrict__ grad_records) {
     extern __shared__ __align__(128) unsigned char s_dyn[];
     float* s_sh = reinterpret_cast<float*>(s_dyn);
     uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_dyn + PROJ_THREADS * SH_ROW_F * 4) + (threadIdx.x >> 5);
@@ -324,6 +325,13 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
             rx = ry = 0;
         }
         reinterpret_cast<int2*>(radii)[g] = make_int2(rx, ry);
+        // what the caller would otherwise produce with two more launches per view: `visibility_filter = radii > 0`
+        // (gsplat_backend.py:206-208) and the zeroed 48-B cotangent record the backward blend accumulates into
+        if (visibility != nullptr) visibility[g] = make_uchar2(rx > 0, ry > 0);
+        if (grad_records != nullptr) {
+            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+            grad_records[3 * g] = z; grad_records[3 * g + 1] = z; grad_records[3 * g + 2] = z;
+        }
         float4* rec = reinterpret_cast<float4*>(splats) + 3 * g;
         rec[0] = r0;
         tiles_per_gauss[g] = ntiles;
@@ -718,9 +726,11 @@ static int project_fwd_impl(bool raw, const float* means, const float* quats, co
                                    const float* opacities, const float* shs, int sh_coeffs, int sh_degree,
                                    int64_t N, const float* cam_host, const float* cam_dev, int width, int height,
                                    int32_t* radii, float* splats, int32_t* tiles_per_gauss, int64_t* block_sums,
-                                   uint32_t* depth_keys, int32_t* gauss_ids, int32_t* tile_grid, void* stream) {
+                                   uint32_t* depth_keys, int32_t* gauss_ids, int32_t* tile_grid, uint8_t* visibility,
+                                   float* grad_records, void* stream) {
     B200_REQUIRE(N >= 0 && width > 0 && height > 0, "bad sizes");
     B200_REQUIRE(sh_args_ok(sh_coeffs, sh_degree), "sh_degree/sh_coeffs mismatch");
+    B200_REQUIRE(((uintptr_t)grad_records & 15) == 0 && ((uintptr_t)visibility & 1) == 0, "misaligned auxiliary output");
     if (tile_grid != nullptr) {
         const size_t cells = (size_t)((width + TILE - 1) / TILE + 1) * (size_t)((height + TILE - 1) / TILE + 1);
         cudaMemsetAsync(tile_grid, 0, cells * sizeof(int32_t), (cudaStream_t)stream);
@@ -740,7 +750,8 @@ static int project_fwd_impl(bool raw, const float* means, const float* quats, co
     if (cam_g == nullptr) return B200_ECUDA;
     // BULK staging of the SH rows needs 16-B aligned rows; the dynamic shared-memory limit is raised once per instantiation
     const bool bulk = SH_BULK && sh_degree >= 0 && vec_ok != 0;
-#define FWD_ARGS means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, cam_g
+#define FWD_ARGS means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, cam_g, \
+                 reinterpret_cast<uchar2*>(visibility), reinterpret_cast<float4*>(grad_records)
 #define LAUNCH_B(D, R) do { \
         static bool attr_set[B200_MAX_DEVICES] = {}; \
         if (b200_first_use_on_device(attr_set)) cudaFuncSetAttribute(project_sh_fwd_kernel<D, R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SH_BULK_SMEM); \
@@ -766,18 +777,21 @@ extern "C" int b200_project_sh_fwd(const float* means, const float* quats, const
                                    const float* shs, int sh_coeffs, int sh_degree, int64_t N, const float* cam_host,
                                    const float* cam_dev, int width, int height, int32_t* radii, float* splats,
                                    int32_t* tiles_per_gauss, int64_t* block_sums, uint32_t* depth_keys, int32_t* gauss_ids,
-                                   int32_t* tile_grid, void* stream) {
+                                   int32_t* tile_grid, uint8_t* visibility, float* grad_records, void* stream) {
     return project_fwd_impl(false, means, quats, scales, opacities, shs, sh_coeffs, sh_degree, N, cam_host, cam_dev, width,
-                            height, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, stream);
+                            height, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, visibility,
+                            grad_records, stream);
 }
 
 extern "C" int b200_project_sh_fwd_raw(const float* xyz, const float* rotation, const float* scaling, const float* opacity,
                                        const float* features, int sh_coeffs, int sh_degree, int64_t N, const float* cam_host,
                                        const float* cam_dev, int width, int height, int32_t* radii, float* splats,
                                        int32_t* tiles_per_gauss, int64_t* block_sums, uint32_t* depth_keys,
-                                       int32_t* gauss_ids, int32_t* tile_grid, void* stream) {
+                                       int32_t* gauss_ids, int32_t* tile_grid, uint8_t* visibility, float* grad_records,
+                                       void* stream) {
     return project_fwd_impl(true, xyz, rotation, scaling, opacity, features, sh_coeffs, sh_degree, N, cam_host, cam_dev, width,
-                            height, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, stream);
+                            height, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, visibility,
+                            grad_records, stream);
 }
 
 static int project_bwd_impl(int mode, const float* means, const float* quats, const float* scales,

@@ -21,6 +21,26 @@ def shard_views(n_views: int, rank: int, world_size: int) -> List[int]:
     return list(range(rank, n_views, world_size))
 
 
+def balance_views(costs: Sequence[float], world_size: int, per_rank: int = 0) -> List[List[int]]:
+    """Assign views to ranks so that the per-rank sums of ``costs`` (e.g. last step's intersection count M of each
+    camera) are as equal as greedy longest-processing-time-first gets them; ``per_rank`` > 0 caps the number of views a
+    rank may take (weak scaling: exactly ``per_rank`` each when ``len(costs) == world_size * per_rank``).  Deterministic:
+    every rank computes the same assignment from the same costs.  A step ends at the slowest rank, so the spread of the
+    per-rank sums is what the all-reduce waits for."""
+    n = len(costs)
+    cap = per_rank if per_rank > 0 else n
+    if world_size * cap < n:
+        raise ValueError("balance_views: world_size * per_rank < number of views")
+    order = sorted(range(n), key=lambda i: (-float(costs[i]), i))
+    load = [0.0] * world_size
+    out: List[List[int]] = [[] for _ in range(world_size)]
+    for i in order:
+        r = min((r for r in range(world_size) if len(out[r]) < cap), key=lambda r: (load[r], r))
+        out[r].append(i)
+        load[r] += float(costs[i])
+    return [sorted(v) for v in out]
+
+
 def allreduce_gradients(params: Iterable[torch.Tensor], n_global_views: int, group=None,
                         flat: torch.Tensor = None) -> torch.Tensor:
     """Sum-all-reduce every ``p.grad`` and scale by 1/n_global_views, so the result is the gradient of the MEAN

@@ -126,7 +126,7 @@ def _sort_scratch(M: int, dev) -> torch.Tensor:
 
 def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional[int], cam, width: int,
                     height: int, keep_unsorted: bool = False, method: str = "auto",
-                    with_isect_ids: bool = False, raw: bool = False) -> Dict[str, torch.Tensor]:
+                    with_isect_ids: bool = False, raw: bool = False, want_grad_records: bool = False) -> Dict[str, torch.Tensor]:
     """Stages 1-2 (projection+SH, tile binning, radix sort, tile ranges).  One host sync (reads M).
 
     method "keys64": literal gsplat formulation — emit (tile<<32|depth) int64 keys, sort M pairs.
@@ -175,14 +175,19 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
         dkeys_a = torch.empty(max(N, 1), dtype=torch.int32, device=dev)
         gids_a = torch.empty(max(N, 1), dtype=torch.int32, device=dev)
     project_fwd = lib.b200_project_sh_fwd_raw if raw else lib.b200_project_sh_fwd  # raw: activations fused in
+    # auxiliary outputs of the projection kernel: visibility_filter (= radii > 0) and, when a backward pass will follow,
+    # the zero-initialised cotangent records it accumulates into — two eager torch launches per view otherwise
+    visibility = torch.empty(N, 2, dtype=torch.bool, device=dev)
+    grad_records = torch.empty(N, _lib.SPLAT_FLOATS, dtype=torch.float32, device=dev) if want_grad_records else None
     with _stage("project_sh_fwd"):
         check(project_fwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors),
                                       sh_coeffs, deg, N, None, _ptr(cam), width, height, _ptr(radii), _ptr(splats),
                                       _ptr(tiles_per_gauss), None if split else _ptr(block_sums),  # split: recounted in depth order
                                       _ptr(dkeys_a) if split else None, _ptr(gids_a) if split else None,
-                                      _ptr(tile_grid), st),
+                                      _ptr(tile_grid), _ptr(visibility), _ptr(grad_records), st),
               "b200_project_sh_fwd", kernels=1 if N > 0 else 0)
-    out = dict(radii=radii, splats=splats, tiles_per_gauss=tiles_per_gauss, tile_w=tile_w, tile_h=tile_h)
+    out = dict(radii=radii, splats=splats, tiles_per_gauss=tiles_per_gauss, tile_w=tile_w, tile_h=tile_h,
+               visibility=visibility, grad_records=grad_records)
     offsets = torch.empty(n_tiles, dtype=torch.int32, device=dev)
     in_b = C.c_int(0)
     if not split:
@@ -330,9 +335,10 @@ class RasterizeSplats(torch.autograd.Function):
         dev = means.device
         if grad_into is not None and not raw:
             raise ValueError("grad_into needs raw=True")
+        needs_grad = any(ctx.needs_input_grad[:5]) or grad_into is not None
         with torch.cuda.device(dev):
             b = project_and_bin(means, quats, scales, opacities, colors, sh_degree, cam, width, height,
-                                method=method, with_isect_ids=with_isect_ids, raw=raw)
+                                method=method, with_isect_ids=with_isect_ids, raw=raw, want_grad_records=needs_grad)
             if b["isect_ids"] is None:
                 b["isect_ids"] = torch.empty(0, dtype=torch.int64, device=dev)
             nch = _NCH[chset]
@@ -347,11 +353,14 @@ class RasterizeSplats(torch.autograd.Function):
         ctx.save_for_backward(means, quats, scales, opacities, colors, b["radii"], b["splats"], b["flatten_ids"],
                               b["isect_offsets"], alpha, last_ids)
         ctx.cfg = (cam, width, height, sh_degree, chset, bg, n_bg, b["M"], raw, grad_into)
+        # zero-initialised cotangent records written by the projection kernel; consumed by the FIRST backward of this node
+        # (a second one, retain_graph=True, allocates its own)
+        ctx.grad_records = b["grad_records"]
         ctx.set_materialize_grads(False)  # unused outputs hand backward() None instead of freshly zero-filled tensors
         ctx.mark_non_differentiable(b["radii"], b["splats"], b["tiles_per_gauss"], b["isect_ids"],
-                                    b["flatten_ids"], b["isect_offsets"], last_ids)
+                                    b["flatten_ids"], b["isect_offsets"], last_ids, b["visibility"])
         return (render, alpha, b["radii"], b["splats"], b["tiles_per_gauss"], b["isect_ids"], b["flatten_ids"],
-                b["isect_offsets"], last_ids)
+                b["isect_offsets"], last_ids, b["visibility"])
 
     @staticmethod
     @torch.amp.custom_bwd(device_type="cuda")
@@ -368,7 +377,9 @@ class RasterizeSplats(torch.autograd.Function):
             v_alpha = v_alpha.to(torch.float32).contiguous()
         with torch.cuda.device(dev):
             st = _stream()
-            v_splats = torch.zeros(N, _lib.SPLAT_FLOATS, dtype=torch.float32, device=dev)
+            v_splats, ctx.grad_records = ctx.grad_records, None
+            if v_splats is None:
+                v_splats = torch.zeros(N, _lib.SPLAT_FLOATS, dtype=torch.float32, device=dev)
             with _stage("raster_bwd"):
                 check(lib.b200_raster_bwd(_ptr(splats), _ptr(flatten_ids), _ptr(offsets), M, width, height, chset,
                                           _ptr(bg), n_bg, _ptr(alpha), _ptr(last_ids), _ptr(v_render), _ptr(v_alpha), _ptr(v_splats),
@@ -444,11 +455,11 @@ def _render_one(means, quats, scales, opacities, colors, viewmat, K, width, heig
     cam = make_cam(viewmat, K, int(width), int(height), near_plane, far_plane, eps2d, radius_clip)
     out = RasterizeSplats.apply(means, quats, scales, opacities, colors, cam, int(width), int(height), sh_degree,
                                 chset, bg, with_isect_ids, method, raw, grad_into)
-    render, alpha, radii, splats, tiles_per_gauss, isect_ids, flatten_ids, offsets, last_ids = out
+    render, alpha, radii, splats, tiles_per_gauss, isect_ids, flatten_ids, offsets, last_ids, visibility = out
     if render_mode in ("ED", "RGB+ED"):
         render = torch.cat([render[..., :-1], render[..., -1:] / alpha.clamp(min=1e-10)], dim=-1)
     return render, alpha, dict(radii=radii, splats=splats, tiles_per_gauss=tiles_per_gauss, isect_ids=isect_ids,
-                               flatten_ids=flatten_ids, isect_offsets=offsets, last_ids=last_ids)
+                               flatten_ids=flatten_ids, isect_offsets=offsets, last_ids=last_ids, visibility=visibility)
 
 
 def rasterization(means: torch.Tensor, quats: torch.Tensor, scales: torch.Tensor, opacities: torch.Tensor,
@@ -514,6 +525,7 @@ def rasterization(means: torch.Tensor, quats: torch.Tensor, scales: torch.Tensor
         "flatten_ids": metas[0]["flatten_ids"] if Ccam == 1 else [m["flatten_ids"] for m in metas],
         "isect_offsets": _stk("isect_offsets"),
         "last_ids": _stk("last_ids"),
+        "visibility_filter": _stk("visibility"),  # radii > 0, written by the projection kernel
         "tile_width": tile_w, "tile_height": tile_h, "tile_size": _lib.TILE,
         "width": width, "height": height, "n_cameras": Ccam,
     }

@@ -219,7 +219,7 @@ class GaussianStore(nn.Module):
             grad_into=self.grad_buffers() if (accumulate_grads and torch.is_grad_enabled()) else None)
         out, alpha = renders.squeeze(0), alphas.squeeze(0)  # views both ways (select's backward = zeros + full-image copy)
         result = {"alpha": alpha, "means2d": meta["means2d"][0], "radii": meta["radii"][0]}
-        result["visibility_filter"] = result["radii"] > 0
+        result["visibility_filter"] = meta["visibility_filter"][0]  # = radii > 0, from the projection kernel
         if render_mode == "RGB":
             result["render"] = out
         elif render_mode == "D":

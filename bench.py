@@ -264,9 +264,30 @@ def run_b200(args):
     # drain phase of one view run under the long blend kernels of the other
     vstreams = pkg.ViewStreams(dev, args.view_streams, params_list)
 
-    def my_view(step, v):  # this rank's camera sequence
-        return view_index(step, v, V, rank, world)
+    # Which camera this rank renders as view v of a step.  One GPU: the plain sequence.  N GPUs: the SAME global batch of
+    # N*V cameras per step as the plain sequence, re-dealt to the ranks by `balance_views` on each camera's intersection
+    # count M (measured once below): a step ends at the slowest rank, and cameras differ by ~10 % in M.
+    assignment = {}
+    cam_cost = None
 
+    def my_view(step, v):
+        if world == 1 or cam_cost is None or args.no_balance:
+            return view_index(step, v, V, rank, world)
+        period = 64 // math.gcd(64, world * V)
+        key = step % period
+        if key not in assignment:
+            batch = [(key * world * V + j) % 64 for j in range(world * V)]
+            parts = pkg.balance_views([cam_cost[c] for c in batch], world, V)
+            assignment[key] = [[batch[i] for i in part] for part in parts]
+        return assignment[key][rank][v]
+
+    if world > 1 and not args.no_balance:
+        with torch.no_grad():  # per-camera M, identical on every rank (same scene, same cameras)
+            cam_cost = []
+            for ci in range(64):
+                camb = pkg.make_cam(poses_dev[ci], K, W, H)
+                cam_cost.append(pkg.project_and_bin(leaves["means3D"], leaves["rotations"], leaves["scales"],
+                                                    leaves["opacities"].squeeze(-1).contiguous(), leaves["shs"], deg, camb, W, H)["M"])
     probe = {"on": False, "render": [], "reduce": []}  # CUDA events of the multi-GPU diagnostic pass (not the headline)
 
     def step_device(step):
@@ -596,6 +617,8 @@ def run_b200(args):
         "reference_trainer_it_per_s": (ref_trainer or {}).get("it_per_s"),
         "reference_trainer": ref_trainer,
         "multi_gpu": multi_gpu,
+        "view_assignment": ("one rank" if world == 1 else ("plain order" if args.no_balance else
+                            "balance_views: the step's N*V cameras dealt to the ranks by intersection count M (LPT)")),
         "oracle_pin": gsplat_probe(),
         "e2e": {"value": e2e_val, "unit": "Mpix/s", "h2d_bytes_per_step": V * (W * H * 3 * 4 + 64), "d2h_bytes_per_step": 4,
                 "ms_per_step": ms_e2e / args.steps},
@@ -633,6 +656,8 @@ def main():
     ap.add_argument("--views-per-rank", type=int, default=4)
     ap.add_argument("--view-streams", type=int, default=2,
                     help="CUDA streams the views of a step alternate over (ViewStreams); 1 = one stream")
+    ap.add_argument("--no-balance", action="store_true",
+                    help="N>1: deal the cameras of a step to the ranks in plain order instead of balancing them by M")
     ap.add_argument("--no-reference-trainer", action="store_true",
                     help="skip the leg that times the reference's unmodified _training_step on B200Backend")
     ap.add_argument("--total-views", type=int, default=0,

@@ -87,7 +87,10 @@ int b200_project_sh_fwd(const float* means, const float* quats, const float* sca
                         int64_t N, const float* cam_host, const float* cam_dev, int width, int height,
                         int32_t* radii, float* splats, int32_t* tiles_per_gauss,
                         int64_t* block_sums, uint32_t* depth_keys, int32_t* gauss_ids,
-                        int32_t* tile_grid, void* stream);
+                        int32_t* tile_grid, uint8_t* visibility, float* grad_records, void* stream);
+/* Two optional auxiliary outputs (NULL = skip) that spare the caller two launches per view:
+ *   visibility[N,2]  uint8 = radii > 0, the `visibility_filter` of gsplat_backend.py:206-208;
+ *   grad_records[N,12] fp32 (16-B aligned) = zeros: the cotangent records b200_raster_bwd accumulates into. */
 
 /* ---- stage 2a: exclusive scan of block sums; writes block_offsets[nblocks] and total[1] -------
  * (the cumsum half of gsplat isect_tiles).  Single CTA; nblocks = b200_project_blocks(N). */
@@ -216,7 +219,7 @@ int b200_project_sh_fwd_raw(const float* xyz, const float* rotation, const float
                             int64_t N, const float* cam_host, const float* cam_dev, int width, int height,
                             int32_t* radii, float* splats, int32_t* tiles_per_gauss,
                             int64_t* block_sums, uint32_t* depth_keys, int32_t* gauss_ids,
-                            int32_t* tile_grid, void* stream);
+                            int32_t* tile_grid, uint8_t* visibility, float* grad_records, void* stream);
 int b200_project_sh_bwd_raw(const float* xyz, const float* rotation, const float* scaling,
                             const float* opacity, const float* features, int sh_coeffs, int sh_degree,
                             int64_t N, const float* cam_host, const float* cam_dev, int width, int height,

@@ -67,3 +67,21 @@ def test_shard_views_partition():
             assert allv == list(range(n))
             sizes = [len(pkg.shard_views(n, r, w)) for r in range(w)]
             assert max(sizes) - min(sizes) <= 1
+
+
+def test_balance_views_is_deterministic_capped_and_balanced():
+    import importlib
+    pkg = importlib.import_module("3d-gaussian-splatting_b200")
+    costs = sorted([19.5, 17.8, 17.7, 18.9, 18.1, 19.9, 17.2, 18.4, 19.1, 17.9, 18.8, 18.0, 19.3, 17.5, 18.6, 18.2], reverse=True)
+    parts = pkg.balance_views(costs, 4, per_rank=4)
+    assert sorted(i for p in parts for i in p) == list(range(16)) and all(len(p) == 4 for p in parts)
+    assert parts == pkg.balance_views(list(costs), 4, per_rank=4)
+    loads = [sum(costs[i] for i in p) for p in parts]
+    plain = [sum(costs[r * 4: r * 4 + 4]) for r in range(4)]
+    assert max(loads) - min(loads) <= max(plain) - min(plain) and max(loads) - min(loads) < 1.0
+    # uncapped: any split; over-subscribed cap: an error
+    parts = pkg.balance_views([5, 1, 1, 1, 1, 1], 2)
+    assert sorted(sum(([i] for p in parts for i in p), [])) == list(range(6)) and {len(p) for p in parts} == {1, 5}
+    import pytest as _pt
+    with _pt.raises(ValueError):
+        pkg.balance_views([1, 2, 3], 2, per_rank=1)
