@@ -32,6 +32,7 @@ SIGNATURES = {
     "b200_project_blocks": (_l, [_l]),
     "b200_cam_pack": (_i, [_p, _p, C.c_float, C.c_float, C.c_float, C.c_float, _i, _i, _p, _p]),
     "b200_project_sh_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "b200_tile_count": (_i, [_p, _p, _l, _i, _i, _p, _p]),
     "b200_tile_prep_max_cells": (_z, []),
     "b200_tile_prep": (_i, [_p, _i, _i, _p, _p, _p, _p]),
     "b200_sort_pairs_k16_prepared": (_i, [_p, _p, _p, _p, _l, _i, _p, _p, _z, _p, _p]),

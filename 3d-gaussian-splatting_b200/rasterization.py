@@ -13,6 +13,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 from typing import Dict, Optional, Tuple
 
 import torch
@@ -97,6 +98,9 @@ def _pinned_scalar(dev: torch.device) -> torch.Tensor:
 
 
 _SIDE_STREAMS = {}
+# True: the tile-corner grid is built by b200_tile_count on the side stream (under the depth sort) instead of by four
+# scattered REDs per Gaussian inside the projection kernel.  B200_GRID_IN_PROJECTION=1 restores the round-1 placement.
+GRID_ON_SIDE_STREAM = os.environ.get("B200_GRID_IN_PROJECTION", "0") != "1"
 
 
 def _side_stream(dev: torch.device) -> torch.cuda.Stream:
@@ -184,7 +188,7 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
                                       sh_coeffs, deg, N, None, _ptr(cam), width, height, _ptr(radii), _ptr(splats),
                                       _ptr(tiles_per_gauss), None if split else _ptr(block_sums),  # split: recounted in depth order
                                       _ptr(dkeys_a) if split else None, _ptr(gids_a) if split else None,
-                                      _ptr(tile_grid), _ptr(visibility), _ptr(grad_records), st),
+                                      None if GRID_ON_SIDE_STREAM else _ptr(tile_grid), _ptr(visibility), _ptr(grad_records), st),
               "b200_project_sh_fwd", kernels=1 if N > 0 else 0)
     out = dict(radii=radii, splats=splats, tiles_per_gauss=tiles_per_gauss, tile_w=tile_w, tile_h=tile_h,
                visibility=visibility, grad_records=grad_records)
@@ -233,6 +237,10 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
         m_host = _pinned_scalar(dev)
         m_ready = torch.cuda.Event()
         with torch.cuda.stream(side):
+            if GRID_ON_SIDE_STREAM:  # the corner grid is counted here, not inside the projection kernel (b200_tile_count)
+                with _stage("tile_count"):
+                    check(lib.b200_tile_count(_ptr(splats), _ptr(radii), N, width, height, _ptr(tile_grid), side.cuda_stream),
+                          "b200_tile_count", kernels=1 if N > 0 else 0)
             with _stage("tile_prep"):
                 check(lib.b200_tile_prep(_ptr(tile_grid), width, height, _ptr(offsets), _ptr(total_prep), _ptr(digit_base),
                                          side.cuda_stream), "b200_tile_prep")

@@ -270,9 +270,21 @@ class GaussianStore(nn.Module):
                           optimizer=None, clone_extent_ratio: float = 0.1, prune_extent_ratio: float = 2.0,
                           max_gaussians: int = None) -> Dict:
         """gaussian_model.py:110-231 — same arguments, same statistics dict, same resulting population (row order,
-        values, spliced Adam moments; the split noise is drawn with the same ``torch.randn_like`` call), but the
-        population change is ONE gather over the flat buffers (``b200_store_gather``) instead of a chain of
-        ``torch.cat`` / mask copies per attribute and per optimiser buffer.  ``optimizer``: a :class:`StoreAdam`."""
+        values, spliced Adam moments; the split noise is drawn with the same ``torch.randn_like`` call on the same
+        shape), but decided and moved ON THE DEVICE with ONE host read-back:
+
+        * the clone / split / prune decisions are element-wise masks over the N Gaussians; the population cap
+          (``_top_k_mask_by_grad``, gaussian_model.py:233-249) is a rank threshold from one stable descending sort of
+          the candidates' gradient norms — the reference's ``torch.topk`` with k in the hundred-thousands is a 40-60 ms
+          call at 3 M Gaussians, the sort ~1 ms;
+        * the reference builds the new population in three rounds ([originals | clones] -> minus the split ones, plus
+          2 x children -> minus the pruned ones), each a chain of ``cat`` / mask copies over six tensors and two
+          optimiser buffers.  Here the final population is addressed directly: a prefix sum over the four candidate
+          segments [kept originals | clones | children #1 | children #2] with the prune decision folded in gives every
+          survivor its final row, the sizes come back in one 7-integer read, and ``b200_store_gather`` moves
+          parameters and both moments once.
+
+        ``optimizer``: a :class:`StoreAdam`."""
         n0 = self._n
         dev = self.flat.device
         stats = {"cloned": 0, "split": 0, "pruned": 0, "n_before": n0, "capped": False}
@@ -283,56 +295,72 @@ class GaussianStore(nn.Module):
         hot = (grads_norm >= grads_threshold) & (opacity > min_opacity)
         clone_mask = hot & (max_scale <= extent * clone_extent_ratio)
         split_mask = hot & (max_scale > extent * clone_extent_ratio)
+        n_comb = torch.zeros((), dtype=torch.int64, device=dev)
+        n_allowed = None
         if max_gaussians is not None and n0 >= int(max_gaussians):
             clone_mask = torch.zeros_like(clone_mask)
             split_mask = torch.zeros_like(split_mask)
             stats["capped"] = True
         elif max_gaussians is not None:
+            # keep the n_allowed candidates with the largest gradient norm.  When there are no more than n_allowed of
+            # them every candidate ranks below n_allowed and the masks are unchanged, so no branch on a device value
             n_allowed = int(max_gaussians) - n0
-            if int(clone_mask.sum().item()) + int(split_mask.sum().item()) > n_allowed:
-                stats["capped"] = True
-                combined = clone_mask | split_mask
-                keep = torch.zeros_like(combined)
-                if n_allowed > 0:  # _top_k_mask_by_grad (gaussian_model.py:233-249)
-                    idx = combined.nonzero(as_tuple=False).view(-1)
-                    keep[idx[torch.topk(grads_norm[idx], k=n_allowed).indices]] = True
-                clone_mask, split_mask = clone_mask & keep, split_mask & keep
-        clone_idx = clone_mask.nonzero(as_tuple=False).view(-1)
-        split_idx = split_mask.nonzero(as_tuple=False).view(-1)
-        keep_idx = (~split_mask).nonzero(as_tuple=False).view(-1)
-        n_k, n_c, n_s = int(keep_idx.numel()), int(clone_idx.numel()), int(split_idx.numel())
-        stats["cloned"], stats["split"] = n_c, n_s
-        # population after clone + split: [originals minus the split ones | clones | 2 x children]
-        src = torch.cat([keep_idx, clone_idx, split_idx, split_idx])
-        state = torch.cat([torch.ones(n_k, dtype=torch.bool, device=dev), torch.zeros(n_c + 2 * n_s, dtype=torch.bool, device=dev)])
-        scale_all = max_scale[src]
-        child_xyz = child_scaling = None
-        if n_s > 0:  # _split_gaussians (gaussian_model.py:278-312), same arithmetic and the same randn call
-            child_scaling = self.scaling[split_idx].repeat(2, 1) - torch.log(torch.tensor(1.6, device=dev))
-            scales = torch.exp(child_scaling)
-            xyz_rep = self.xyz[split_idx].repeat(2, 1)
-            child_xyz = xyz_rep + torch.randn_like(xyz_rep) * scales[:, :3]
-            scale_all = torch.cat([scale_all[: n_k + n_c], scales.amax(dim=-1)])
-        low_op = opacity[src] < min_opacity
-        too_big = scale_all > extent * prune_extent_ratio
-        prune = low_op | too_big
-        n_pruned = int(prune.sum().item())
-        stats["pruned"] = n_pruned
-        stats["pruned_low_op"] = int(low_op.sum().item()) if n_pruned else 0
-        stats["pruned_too_big"] = int(too_big.sum().item()) if n_pruned else 0
-        sel = (~prune).nonzero(as_tuple=False).view(-1)
+            combined = clone_mask | split_mask
+            n_comb = combined.sum()
+            order = torch.argsort(torch.where(combined, grads_norm, torch.full_like(grads_norm, float("-inf"))),
+                                  descending=True, stable=True)
+            keep = torch.zeros_like(combined)
+            keep[order[:max(n_allowed, 0)]] = True
+            clone_mask, split_mask = clone_mask & keep, split_mask & keep
+        # prune decision on the post-densify population (gaussian_model.py:190-213): clones carry their source's values,
+        # children the source's opacity and its log-scales minus log 1.6 (gaussian_model.py:299-300)
+        child_scaling_all = self.scaling - torch.log(torch.tensor(1.6, device=dev))
+        child_scales_all = torch.exp(child_scaling_all)
+        low_op = opacity < min_opacity
+        big_o = max_scale > extent * prune_extent_ratio
+        big_c = child_scales_all.amax(dim=-1) > extent * prune_extent_ratio
+        prune_o, prune_c = low_op | big_o, low_op | big_c
+        stay = ~split_mask
+        segs = (stay, clone_mask, split_mask, split_mask)  # [kept originals | clones | children #1 | children #2]
+        prunes = (prune_o, prune_o, prune_c, prune_c)
+        flags = torch.cat([m & ~p for m, p in zip(segs, prunes)])
+        csum = torch.cumsum(flags.to(torch.int32), dim=0)
+        cnt = lambda m: m.sum()  # noqa: E731
+        counts = torch.stack([
+            csum[-1].to(torch.int64) if n0 > 0 else torch.zeros((), dtype=torch.int64, device=dev),
+            cnt(clone_mask), cnt(split_mask),
+            cnt(stay & prune_o) + cnt(clone_mask & prune_o) + 2 * cnt(split_mask & prune_c),
+            cnt(stay & low_op) + cnt(clone_mask & low_op) + 2 * cnt(split_mask & low_op),
+            cnt(stay & big_o) + cnt(clone_mask & big_o) + 2 * cnt(split_mask & big_c),
+            n_comb,
+        ])
+        n_new, n_c, n_s, n_pruned, n_low, n_big, n_cand = (int(x) for x in counts.tolist())  # THE host read-back
+        stats["cloned"], stats["split"], stats["pruned"] = n_c, n_s, n_pruned
+        stats["pruned_low_op"] = n_low if n_pruned else 0
+        stats["pruned_too_big"] = n_big if n_pruned else 0
+        if n_allowed is not None and n_cand > n_allowed:
+            stats["capped"] = True
         if n_c == 0 and n_s == 0 and n_pruned == 0:
             self.xyz_gradient_accum.zero_()
             self.xyz_gradient_count.zero_()
             stats["n_after"] = n0
             return stats
-        self._rebuild(src[sel], state[sel], optimizer)
-        if n_s > 0:  # children: position in the new population, index into the child arrays
-            is_child = sel >= (n_k + n_c)
-            pos = is_child.nonzero(as_tuple=False).view(-1)
-            child = sel[pos] - (n_k + n_c)
-            self.xyz.data[pos] = child_xyz[child]
-            self.scaling.data[pos] = child_scaling[child]
+        # final row of every survivor (dump slot n_new for the rest), then one gather
+        idx4 = torch.arange(n0, device=dev).repeat(4)
+        dst = torch.where(flags, csum.to(torch.int64) - 1, torch.full((), n_new, dtype=torch.int64, device=dev))
+        src_rows = torch.empty(n_new + 1, dtype=torch.int64, device=dev).scatter_(0, dst, idx4)[:n_new]
+        seg4 = torch.arange(4, device=dev, dtype=torch.uint8).repeat_interleave(n0)
+        seg_new = torch.empty(n_new + 1, dtype=torch.uint8, device=dev).scatter_(0, dst, seg4)[:n_new]
+        old_xyz = self.xyz.detach()
+        split_ord = torch.cumsum(split_mask.to(torch.int64), dim=0) - 1  # j-th split Gaussian in index order
+        self._rebuild(src_rows, seg_new == 0, optimizer)
+        if n_s > 0:  # _split_gaussians (gaussian_model.py:278-312): same arithmetic, the same randn call
+            noise = torch.randn(2 * n_s, 3, device=dev, dtype=old_xyz.dtype)  # == randn_like(xyz[idx].repeat(2, 1))
+            is_child = seg_new >= 2
+            row = (split_ord[src_rows] + (seg_new.to(torch.int64) - 2).clamp_(min=0) * n_s).clamp_(min=0)
+            child_xyz = old_xyz[src_rows] + noise[row] * child_scales_all[src_rows]
+            self.xyz.data.copy_(torch.where(is_child[:, None], child_xyz, self.xyz.data))
+            self.scaling.data.copy_(torch.where(is_child[:, None], child_scaling_all[src_rows], self.scaling.data))
         stats["n_after"] = self._n
         return stats
 

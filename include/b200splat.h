@@ -164,6 +164,12 @@ int b200_isect_ids_from_offsets(const int32_t* flatten_ids, const int32_t* isect
  *   digit_base[2*256] = exclusive digit offsets of the two 8-bit passes of the tile-key sort
  * come from one single-CTA kernel; b200_sort_pairs_k16_prepared then skips its histogram pass.
  * Needs (tile_w+1)*(tile_h+1) <= b200_tile_prep_max_cells() (the grid is staged in shared memory). */
+/* The corner-difference grid built OUTSIDE the projection kernel (call b200_project_sh_fwd with tile_grid == NULL): a few
+ * persistent CTAs recompute every visible Gaussian's tile rectangle from the stored means2d / radii (same fp32
+ * operations), accumulate the +1/-1 corners in a shared-memory copy of the grid and flush it once.  tile_grid is zeroed
+ * by the call.  Runs on a side stream under the depth sort (rasterization.py). */
+int b200_tile_count(const float* splats, const int32_t* radii, int64_t N, int width, int height, int32_t* tile_grid,
+                    void* stream);
 size_t b200_tile_prep_max_cells(void);
 int b200_tile_prep(const int32_t* tile_grid, int width, int height, int32_t* offsets, int64_t* total,
                    uint32_t* digit_base, void* stream);
