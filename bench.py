@@ -555,6 +555,7 @@ def run_b200(args):
         "bin_coarse": M * 36 + N * 16,
         "sort_pairs": M * 24,
         "tile_ranges": M * 8,
+        "tile_count": N * 16,             # radii + means2d of every Gaussian (corner grid, side stream)
         "tile_prep": ((W + 15) // 16 + 1) * ((H + 15) // 16 + 1) * 4 + ((W + 15) // 16) * ((H + 15) // 16) * 4,
         "sort_depth": N * (4 + 4 * 16),   # one histogram read + four onesweep passes over (u32 key, i32 id)
         "bin_scan": N * 8,
@@ -578,8 +579,8 @@ def run_b200(args):
         except Exception:
             pass
         roofline = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": round(ach / hbm, 4),
-                    "traffic": traffic, "binding_resource": "FP32/SFU issue slots (not HBM) for raster_fwd / raster_bwd, see "
-                    "profiles/ncu_r01_summary.md" if dom.startswith("raster") else "HBM", "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
+                    "traffic": traffic, "binding_resource": "FP32/SFU issue slots (not HBM) for raster_fwd / raster_bwd: 77-79 % issue-active, per-line "
+                    "instruction table and lower bound in profiles/ncu_r02_summary.md + profiles/r02/raster_bwd_lines.md" if dom.startswith("raster") else "HBM", "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})",
                     "share_of_step": round(per_view_ms[dom] / sum(per_view_ms.values()), 3), "stages": stages}
         if timer_one is not None:
             t1, c1 = timer_one.totals_ms(), timer_one.counts()
