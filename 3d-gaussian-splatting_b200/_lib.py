@@ -31,7 +31,7 @@ SIGNATURES = {
     "b200_last_error": (C.c_char_p, []),
     "b200_project_blocks": (_l, [_l]),
     "b200_cam_pack": (_i, [_p, _p, C.c_float, C.c_float, C.c_float, C.c_float, _i, _i, _p, _p]),
-    "b200_project_sh_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "b200_project_sh_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "b200_tile_count": (_i, [_p, _p, _l, _i, _i, _p, _p]),
     "b200_tile_prep_max_cells": (_z, []),
     "b200_tile_prep": (_i, [_p, _i, _i, _p, _p, _p, _p]),
@@ -54,7 +54,7 @@ SIGNATURES = {
     "b200_raster_fwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _p, _i, _p, _p, _p, _p]),
     "b200_raster_bwd": (_i, [_p, _p, _p, _l, _i, _i, _i, _p, _i, _p, _p, _p, _p, _p, _p]),
     "b200_project_sh_bwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p]),
-    "b200_project_sh_fwd_raw": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "b200_project_sh_fwd_raw": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "b200_project_sh_bwd_raw": (_i, [_p, _p, _p, _p, _p, _i, _i, _l, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _i, _p]),
     "b200_l1_ssim_fwd_bwd": (_i, [_p, _p, _i, _i, C.c_float, C.c_float, _p, _p, _p]),
     "b200_adam_step": (_i, [_p, _p, _p, _p, _l, _p, _i, _i, C.c_float, C.c_float, C.c_float, _p]),

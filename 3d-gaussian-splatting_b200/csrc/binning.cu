@@ -368,16 +368,26 @@ __global__ void isect_ids_kernel(const uint16_t* __restrict__ tile_keys, const i
 // (Gaussian, supertile) pairs of every 1024-Gaussian chunk.  Embarrassingly parallel: the two dependent gathers
 // (perm -> radii / means2d) of one CTA overlap with those of all the others; nothing waits on a neighbour.
 __global__ void __launch_bounds__(EC_THREADS)
-coarse_count_kernel(const float* __restrict__ splats, const int32_t* __restrict__ radii, const int32_t* __restrict__ perm,
-                    int64_t N, int tile_w, int tile_h, uint2* __restrict__ rect_sorted, uint32_t* __restrict__ chunk_sums) {
+coarse_count_kernel(const float* __restrict__ splats, const int32_t* __restrict__ radii, const uint2* __restrict__ rects,
+                    const int32_t* __restrict__ perm, int64_t N, int tile_w, int tile_h, uint2* __restrict__ rect_sorted,
+                    uint32_t* __restrict__ chunk_sums) {
     __shared__ int s_warp[EC_THREADS / 32];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int64_t i = (int64_t)blockIdx.x * EC_THREADS + tid;
     int cnt = 0;
     if (i < N) {
         const int g = __ldg(perm + i);
-        const int2 rad = __ldg(reinterpret_cast<const int2*>(radii) + g);
         uint2 packed = make_uint2(0u, 0u);
+        if (rects != nullptr) {  // packed by the projection kernel: one 8-byte gather
+            packed = __ldg(rects + g);
+            if (packed.x != 0u || packed.y != 0u) {
+                const int minx = (int)(packed.x & 0xFFFFu), maxx = (int)(packed.x >> 16);
+                const int miny = (int)(packed.y & 0xFFFFu), maxy = (int)(packed.y >> 16);
+                cnt = (((maxx - 1) >> ST_SHIFT) - (minx >> ST_SHIFT) + 1) * (((maxy - 1) >> ST_SHIFT) - (miny >> ST_SHIFT) + 1);
+            }
+            rect_sorted[i] = packed;
+        }
+        const int2 rad = (rects == nullptr) ? __ldg(reinterpret_cast<const int2*>(radii) + g) : make_int2(0, 0);
         if (rad.x > 0) {  // culled Gaussians carry radii (0, 0) (project_sh_fwd) and sort to the end of perm
             const float2 m2 = __ldg(reinterpret_cast<const float2*>(splats + SPLAT_F * (size_t)g));
             // the tile rectangle, with the same fp32 operations as the projection kernel / the oracle's tile_bounds
@@ -393,7 +403,7 @@ coarse_count_kernel(const float* __restrict__ splats, const int32_t* __restrict_
                 packed = make_uint2((uint32_t)minx | ((uint32_t)maxx << 16), (uint32_t)miny | ((uint32_t)maxy << 16));
             }
         }
-        rect_sorted[i] = packed;
+        if (rects == nullptr) rect_sorted[i] = packed;
     }
     int v = cnt;
 #pragma unroll
@@ -814,7 +824,7 @@ extern "C" size_t b200_bin_coarse_scratch_bytes(int64_t N, int64_t M_cap) {
     return head + b200_sort_scratch_bytes(M_cap);
 }
 
-extern "C" int b200_bin_coarse(const float* splats, const int32_t* radii, const int32_t* tiles_per_gauss, const int32_t* perm,
+extern "C" int b200_bin_coarse(const float* splats, const int32_t* radii, const void* tile_rects, const int32_t* perm,
                                int64_t N, int width, int height, const int32_t* isect_offsets, int64_t M,
                                uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b,
                                int32_t* flatten_ids, void* scratch, size_t scratch_bytes, void* stream) {
@@ -822,7 +832,7 @@ extern "C" int b200_bin_coarse(const float* splats, const int32_t* radii, const 
     B200_REQUIRE(M < ((int64_t)1 << 30), "too many intersections (M >= 2^30)");
     B200_REQUIRE(b200_bin_coarse_supported(width, height), "tile grid outside the coarse path's limits");
     if (N == 0 || M == 0) return B200_OK;
-    B200_REQUIRE(splats && radii && tiles_per_gauss && perm && isect_offsets, "null pointer");
+    B200_REQUIRE(splats && radii && perm && isect_offsets, "null pointer");
     B200_REQUIRE(keys_a && vals_a && keys_b && vals_b && flatten_ids && scratch, "null buffer");
     if (scratch_bytes < b200_bin_coarse_scratch_bytes(N, M)) {
         b200_set_error("b200_bin_coarse: scratch too small (%zu < %zu)", scratch_bytes, b200_bin_coarse_scratch_bytes(N, M));
@@ -853,7 +863,8 @@ extern "C" int b200_bin_coarse(const float* splats, const int32_t* radii, const 
     const int n_sm = (dev >= 0 && dev < B200_MAX_DEVICES && sms[dev] > 0) ? sms[dev] : 148;
     const unsigned grid = (unsigned)min((size_t)min(n_sm * EC_CTAS_PER_SM, EC_THREADS), nchunks);  // persistent CTAs
     (void)ticket;
-    coarse_count_kernel<<<(unsigned)nchunks, EC_THREADS, 0, st>>>(splats, radii, perm, N, tile_w, tile_h, rect_sorted, chunk_sums);
+    coarse_count_kernel<<<(unsigned)nchunks, EC_THREADS, 0, st>>>(splats, radii, reinterpret_cast<const uint2*>(tile_rects), perm, N,
+                                                                  tile_w, tile_h, rect_sorted, chunk_sums);
     emit_coarse_kernel<<<grid, EC_THREADS, (size_t)n_st * 4, st>>>(rect_sorted, perm, N, chunk_sums, st_w, n_st, (uint32_t)M,
                                                                    keys_a, vals_a, st_counts, total);
     coarse_prep_kernel<<<1, 1024, 0, st>>>(st_counts, n_st, st_offsets, digit_base);

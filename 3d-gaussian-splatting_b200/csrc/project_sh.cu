@@ -252,7 +252,7 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
                       int32_t* __restrict__ tiles_per_gauss, int64_t* __restrict__ block_sums,
                       uint32_t* __restrict__ depth_keys, int32_t* __restrict__ gauss_ids,
                       int32_t* __restrict__ tile_grid, const Cam* __restrict__ cam_g,
-                      uchar2* __restrict__ visibility, float4* __restrict__ grad_records) {
+                      uchar2* __restrict__ visibility, float4* __restrict__ grad_records, uint2* __restrict__ tile_rects) {
     extern __shared__ __align__(128) unsigned char s_dyn[];
     float* s_sh = reinterpret_cast<float*>(s_dyn);
     uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_dyn + PROJ_THREADS * SH_ROW_F * 4) + (threadIdx.x >> 5);
@@ -299,6 +299,7 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
         // of queueing behind it.
         float4 r0 = make_float4(0.f, 0.f, 0.f, 0.f), r1 = r0, r2 = r0;
         float inv_det = 0.f;
+        uint2 rect = make_uint2(0u, 0u);
         if (ok) {
             // tile rectangle — same fp32 operations as the oracle's tile_bounds
             float tile_x = P.mx / (float)TILE, tile_y = P.my / (float)TILE;
@@ -309,6 +310,9 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
             int miny = (int)fminf(fmaxf(floorf(tile_y - try_), 0.f), fh);
             int maxy = (int)fminf(fmaxf(ceilf(tile_y + try_), 0.f), fh);
             ntiles = (maxy - miny) * (maxx - minx);
+            // packed tile rectangle: the binning kernels gather ONE 8-byte word per Gaussian behind the depth permutation
+            // instead of radii + means2d (two 32-B sectors)
+            if (ntiles > 0) rect = make_uint2((uint32_t)minx | ((uint32_t)maxx << 16), (uint32_t)miny | ((uint32_t)maxy << 16));
             if (tile_grid != nullptr && ntiles > 0) {
                 // corner differences of the tile rectangle: a 2-D prefix sum (b200_tile_prep) turns the grid
                 // into per-tile intersection counts, i.e. the tile ranges and the radix digit histograms,
@@ -328,6 +332,7 @@ project_sh_fwd_kernel(const float* __restrict__ means, const float* __restrict__
         // what the caller would otherwise produce with two more launches per view: `visibility_filter = radii > 0`
         // (gsplat_backend.py:206-208) and the zeroed 48-B cotangent record the backward blend accumulates into
         if (visibility != nullptr) visibility[g] = make_uchar2(rx > 0, ry > 0);
+        if (tile_rects != nullptr) tile_rects[g] = rect;
         if (grad_records != nullptr) {
             const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
             grad_records[3 * g] = z; grad_records[3 * g + 1] = z; grad_records[3 * g + 2] = z;
@@ -727,8 +732,9 @@ static int project_fwd_impl(bool raw, const float* means, const float* quats, co
                                    int64_t N, const float* cam_host, const float* cam_dev, int width, int height,
                                    int32_t* radii, float* splats, int32_t* tiles_per_gauss, int64_t* block_sums,
                                    uint32_t* depth_keys, int32_t* gauss_ids, int32_t* tile_grid, uint8_t* visibility,
-                                   float* grad_records, void* stream) {
+                                   float* grad_records, void* tile_rects, void* stream) {
     B200_REQUIRE(N >= 0 && width > 0 && height > 0, "bad sizes");
+    B200_REQUIRE(((uintptr_t)tile_rects & 7) == 0, "misaligned tile_rects");
     B200_REQUIRE(sh_args_ok(sh_coeffs, sh_degree), "sh_degree/sh_coeffs mismatch");
     B200_REQUIRE(((uintptr_t)grad_records & 15) == 0 && ((uintptr_t)visibility & 1) == 0, "misaligned auxiliary output");
     if (tile_grid != nullptr) {
@@ -751,7 +757,7 @@ static int project_fwd_impl(bool raw, const float* means, const float* quats, co
     // BULK staging of the SH rows needs 16-B aligned rows; the dynamic shared-memory limit is raised once per instantiation
     const bool bulk = SH_BULK && sh_degree >= 0 && vec_ok != 0;
 #define FWD_ARGS means, quats, scales, opacities, shs, sh_coeffs, vec_ok, N, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, cam_g, \
-                 reinterpret_cast<uchar2*>(visibility), reinterpret_cast<float4*>(grad_records)
+                 reinterpret_cast<uchar2*>(visibility), reinterpret_cast<float4*>(grad_records), reinterpret_cast<uint2*>(tile_rects)
 #define LAUNCH_B(D, R) do { \
         static bool attr_set[B200_MAX_DEVICES] = {}; \
         if (b200_first_use_on_device(attr_set)) cudaFuncSetAttribute(project_sh_fwd_kernel<D, R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SH_BULK_SMEM); \
@@ -777,10 +783,11 @@ extern "C" int b200_project_sh_fwd(const float* means, const float* quats, const
                                    const float* shs, int sh_coeffs, int sh_degree, int64_t N, const float* cam_host,
                                    const float* cam_dev, int width, int height, int32_t* radii, float* splats,
                                    int32_t* tiles_per_gauss, int64_t* block_sums, uint32_t* depth_keys, int32_t* gauss_ids,
-                                   int32_t* tile_grid, uint8_t* visibility, float* grad_records, void* stream) {
+                                   int32_t* tile_grid, uint8_t* visibility, float* grad_records, void* tile_rects,
+                                   void* stream) {
     return project_fwd_impl(false, means, quats, scales, opacities, shs, sh_coeffs, sh_degree, N, cam_host, cam_dev, width,
                             height, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, visibility,
-                            grad_records, stream);
+                            grad_records, tile_rects, stream);
 }
 
 extern "C" int b200_project_sh_fwd_raw(const float* xyz, const float* rotation, const float* scaling, const float* opacity,
@@ -788,10 +795,10 @@ extern "C" int b200_project_sh_fwd_raw(const float* xyz, const float* rotation, 
                                        const float* cam_dev, int width, int height, int32_t* radii, float* splats,
                                        int32_t* tiles_per_gauss, int64_t* block_sums, uint32_t* depth_keys,
                                        int32_t* gauss_ids, int32_t* tile_grid, uint8_t* visibility, float* grad_records,
-                                       void* stream) {
+                                       void* tile_rects, void* stream) {
     return project_fwd_impl(true, xyz, rotation, scaling, opacity, features, sh_coeffs, sh_degree, N, cam_host, cam_dev, width,
                             height, radii, splats, tiles_per_gauss, block_sums, depth_keys, gauss_ids, tile_grid, visibility,
-                            grad_records, stream);
+                            grad_records, tile_rects, stream);
 }
 
 static int project_bwd_impl(int mode, const float* means, const float* quats, const float* scales,

@@ -154,7 +154,8 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
         if method == "split" and (tile_w + 1) * (tile_h + 1) <= int(lib.b200_tile_prep_max_cells()) \
                 and lib.b200_bin_coarse_supported(width, height):
             method = "coarse"
-    coarse = method == "coarse"
+    coarse_gather = method == "coarse-gather"  # "coarse" recomputing the rectangles from radii / means2d (test path)
+    coarse = method in ("coarse", "coarse-gather")
     if coarse:
         if not lib.b200_bin_coarse_supported(width, height) or (tile_w + 1) * (tile_h + 1) > int(lib.b200_tile_prep_max_cells()):
             raise ValueError("binning='coarse' needs a tile grid within b200_bin_coarse_supported / b200_tile_prep limits")
@@ -183,12 +184,14 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
     # the zero-initialised cotangent records it accumulates into — two eager torch launches per view otherwise
     visibility = torch.empty(N, 2, dtype=torch.bool, device=dev)
     grad_records = torch.empty(N, _lib.SPLAT_FLOATS, dtype=torch.float32, device=dev) if want_grad_records else None
+    rects = torch.empty(N, 2, dtype=torch.int32, device=dev) if (coarse and not coarse_gather) else None  # packed tile rectangles
     with _stage("project_sh_fwd"):
         check(project_fwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors),
                                       sh_coeffs, deg, N, None, _ptr(cam), width, height, _ptr(radii), _ptr(splats),
                                       _ptr(tiles_per_gauss), None if split else _ptr(block_sums),  # split: recounted in depth order
                                       _ptr(dkeys_a) if split else None, _ptr(gids_a) if split else None,
-                                      None if GRID_ON_SIDE_STREAM else _ptr(tile_grid), _ptr(visibility), _ptr(grad_records), st),
+                                      None if GRID_ON_SIDE_STREAM else _ptr(tile_grid), _ptr(visibility), _ptr(grad_records),
+                                      _ptr(rects), st),
               "b200_project_sh_fwd", kernels=1 if N > 0 else 0)
     out = dict(radii=radii, splats=splats, tiles_per_gauss=tiles_per_gauss, tile_w=tile_w, tile_h=tile_h,
                visibility=visibility, grad_records=grad_records)
@@ -265,7 +268,7 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
         sb = int(lib.b200_bin_coarse_scratch_bytes(N, M))
         scratch_c = torch.empty(max(sb, 256), dtype=torch.uint8, device=dev)
         with _stage("bin_coarse"):
-            check(lib.b200_bin_coarse(_ptr(splats), _ptr(radii), _ptr(tiles_per_gauss), _ptr(perm), N, width, height,
+            check(lib.b200_bin_coarse(_ptr(splats), _ptr(radii), _ptr(rects), _ptr(perm), N, width, height,
                                       _ptr(offsets), M, _ptr(ck[0]), _ptr(ck[1]), _ptr(ck[2]), _ptr(ck[3]), _ptr(flat_ids),
                                       _ptr(scratch_c), scratch_c.numel(), st), "b200_bin_coarse",
                   kernels=(3 + (2 if n_tiles > 16 * 256 else 1)) if (N > 0 and M > 0) else 0)

@@ -290,11 +290,19 @@ def run_b200(args):
                                                     leaves["opacities"].squeeze(-1).contiguous(), leaves["shs"], deg, camb, W, H)["M"])
     probe = {"on": False, "render": [], "reduce": []}  # CUDA events of the multi-GPU diagnostic pass (not the headline)
 
+    # N > 1: the five gradient tensors are views of ONE flat buffer (distributed.FlatGradients), reduced by one collective
+    # (opt-in: measured at N=2 it costs more — the memset and the first view's in-place add, 0.2 ms — than the one collective
+    # saves, 0.12 ms: 5.42 -> 5.56 ms per step)
+    flat_grads = pkg.FlatGradients(params_list) if (world > 1 and args.flat_grads) else None
+
     def step_device(step):
         """inputs resident in HBM: pose + cotangent on device."""
         nonlocal flat
-        for p in params_list:
-            p.grad = None
+        if flat_grads is not None:
+            flat_grads.begin_step()
+        else:
+            for p in params_list:
+                p.grad = None
         if probe["on"]:
             ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
             ev[0].record()
@@ -307,7 +315,9 @@ def run_b200(args):
         vstreams.join()
         if probe["on"]:
             ev[1].record()
-        if world > 1:
+        if flat_grads is not None:
+            flat_grads.allreduce(world * V)
+        elif world > 1:
             flat = pkg.allreduce_gradients(params_list, world * V, flat=flat)
         if probe["on"]:
             ev[2].record()
@@ -335,8 +345,11 @@ def run_b200(args):
         """through the public backend call with HOST buffers: pose + ground-truth frame uploaded from pinned
         memory every view, L1 + D-SSIM loss, backward, loss read back (what trainer.py:270-281,485-497 does per view)."""
         nonlocal flat
-        for p in params_list:
-            p.grad = None
+        if flat_grads is not None:
+            flat_grads.begin_step()
+        else:
+            for p in params_list:
+                p.grad = None
         losses = []
         vstreams.begin()
         for v in range(V):
@@ -361,7 +374,9 @@ def run_b200(args):
                 losses.append(loss.detach())
                 e2e_state["k"] = k + 1
         vstreams.join()
-        if world > 1:
+        if flat_grads is not None:
+            flat_grads.allreduce(world * V)
+        elif world > 1:
             flat = pkg.allreduce_gradients(params_list, world * V, flat=flat)
         return float(torch.stack(losses).sum().item())  # D2H read of the step's result
 
@@ -618,6 +633,8 @@ def run_b200(args):
         "reference_trainer_it_per_s": (ref_trainer or {}).get("it_per_s"),
         "reference_trainer": ref_trainer,
         "multi_gpu": multi_gpu,
+        "gradient_collective": (None if world == 1 else ("five all-reduces back to back (one per attribute tensor)" if not args.flat_grads else
+                                "ONE all-reduce: the five .grad tensors are views of a flat buffer (FlatGradients)")),
         "view_assignment": ("one rank" if world == 1 else ("plain order" if args.no_balance else
                             "balance_views: the step's N*V cameras dealt to the ranks by intersection count M (LPT)")),
         "oracle_pin": gsplat_probe(),
@@ -657,6 +674,9 @@ def main():
     ap.add_argument("--views-per-rank", type=int, default=4)
     ap.add_argument("--view-streams", type=int, default=2,
                     help="CUDA streams the views of a step alternate over (ViewStreams); 1 = one stream")
+    ap.add_argument("--flat-grads", action="store_true",
+                    help="N>1, drop-in path: make the five .grad tensors views of one flat buffer and reduce it with ONE collective "
+                         "(default: autograd allocates them, five collectives back to back)")
     ap.add_argument("--no-balance", action="store_true",
                     help="N>1: deal the cameras of a step to the ranks in plain order instead of balancing them by M")
     ap.add_argument("--no-reference-trainer", action="store_true",

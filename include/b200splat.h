@@ -87,10 +87,14 @@ int b200_project_sh_fwd(const float* means, const float* quats, const float* sca
                         int64_t N, const float* cam_host, const float* cam_dev, int width, int height,
                         int32_t* radii, float* splats, int32_t* tiles_per_gauss,
                         int64_t* block_sums, uint32_t* depth_keys, int32_t* gauss_ids,
-                        int32_t* tile_grid, uint8_t* visibility, float* grad_records, void* stream);
-/* Two optional auxiliary outputs (NULL = skip) that spare the caller two launches per view:
- *   visibility[N,2]  uint8 = radii > 0, the `visibility_filter` of gsplat_backend.py:206-208;
- *   grad_records[N,12] fp32 (16-B aligned) = zeros: the cotangent records b200_raster_bwd accumulates into. */
+                        int32_t* tile_grid, uint8_t* visibility, float* grad_records, void* tile_rects,
+                        void* stream);
+/* Three optional auxiliary outputs (NULL = skip):
+ *   visibility[N,2]  uint8 = radii > 0, the `visibility_filter` of gsplat_backend.py:206-208 (no compare launch);
+ *   grad_records[N,12] fp32 (16-B aligned) = zeros: the cotangent records b200_raster_bwd accumulates into (no fill launch);
+ *   tile_rects[N] 2 x uint32 = (minx | maxx << 16, miny | maxy << 16), the Gaussian's tile rectangle of SURVEY.md A.3,
+ *     (0, 0) when it touches no tile — what b200_bin_coarse gathers behind the depth permutation (8 B instead of
+ *     radii + means2d). */
 
 /* ---- stage 2a: exclusive scan of block sums; writes block_offsets[nblocks] and total[1] -------
  * (the cumsum half of gsplat isect_tiles).  Single CTA; nblocks = b200_project_blocks(N). */
@@ -145,11 +149,12 @@ int b200_bin_emit_sorted(const float* splats, const int32_t* radii, const int32_
  *   3. the pairs are sorted stably on the supertile bits (one or two 8-bit onesweep passes over M', count on the device);
  *   4. one CTA per supertile, one warp per tile, streams the supertile's list once and compacts the ids covering its
  *      tile into flatten_ids[isect_offsets[tile] ...] in list order (= depth order, ties by ascending Gaussian index).
- * keys_a/vals_a/keys_b/vals_b: M uint32 each (only M' used); scratch: b200_bin_coarse_scratch_bytes(N, M) bytes.
+ * tile_rects: the packed per-Gaussian rectangles written by b200_project_sh_fwd, or NULL (then they are recomputed from
+ * radii / means2d).  keys_a/vals_a/keys_b/vals_b: M uint32 each (only M' used); scratch: b200_bin_coarse_scratch_bytes(N, M).
  * Needs b200_bin_coarse_supported(width, height): <= 65 536 tiles and <= 4096 supertiles. */
 int b200_bin_coarse_supported(int width, int height);
 size_t b200_bin_coarse_scratch_bytes(int64_t N, int64_t M_cap);
-int b200_bin_coarse(const float* splats, const int32_t* radii, const int32_t* tiles_per_gauss, const int32_t* perm,
+int b200_bin_coarse(const float* splats, const int32_t* radii, const void* tile_rects, const int32_t* perm,
                     int64_t N, int width, int height, const int32_t* isect_offsets, int64_t M,
                     uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b,
                     int32_t* flatten_ids, void* scratch, size_t scratch_bytes, void* stream);
@@ -225,7 +230,8 @@ int b200_project_sh_fwd_raw(const float* xyz, const float* rotation, const float
                             int64_t N, const float* cam_host, const float* cam_dev, int width, int height,
                             int32_t* radii, float* splats, int32_t* tiles_per_gauss,
                             int64_t* block_sums, uint32_t* depth_keys, int32_t* gauss_ids,
-                            int32_t* tile_grid, uint8_t* visibility, float* grad_records, void* stream);
+                            int32_t* tile_grid, uint8_t* visibility, float* grad_records, void* tile_rects,
+                            void* stream);
 int b200_project_sh_bwd_raw(const float* xyz, const float* rotation, const float* scaling,
                             const float* opacity, const float* features, int sh_coeffs, int sh_degree,
                             int64_t N, const float* cam_host, const float* cam_dev, int width, int height,

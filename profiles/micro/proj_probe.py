@@ -24,7 +24,7 @@ flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 st = torch.cuda.current_stream().cuda_stream
 def call():
     check(lib.b200_project_sh_fwd(_ptr(p["means3D"]), _ptr(p["rotations"]), _ptr(p["scales"]), _ptr(p["opacities"].reshape(-1)), _ptr(p["shs"]),
-                                  16, deg, N, None, _ptr(cam), W, H, _ptr(radii), _ptr(splats), _ptr(tpg), (None if os.environ.get("NO_BS") else _ptr(bs)), _ptr(dk), _ptr(gi), _ptr(grid), None, None, st), "proj")
+                                  16, deg, N, None, _ptr(cam), W, H, _ptr(radii), _ptr(splats), _ptr(tpg), (None if os.environ.get("NO_BS") else _ptr(bs)), _ptr(dk), _ptr(gi), _ptr(grid), None, None, None, st), "proj")
 for _ in range(5): call()
 tot = 0.0
 for _ in range(reps):

@@ -85,3 +85,39 @@ def test_balance_views_is_deterministic_capped_and_balanced():
     import pytest as _pt
     with _pt.raises(ValueError):
         pkg.balance_views([1, 2, 3], 2, per_rank=1)
+
+
+def _worker_flat(rank, world, port, n_views, out):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    pkg = importlib.import_module("3d-gaussian-splatting_b200")
+    torch.manual_seed(1)
+    params = [torch.randn(7, 3, requires_grad=True), torch.randn(5, requires_grad=True)]
+    views = _views(n_views)
+    fg = pkg.FlatGradients(params)
+    grads = []
+    for _ in range(2):  # two steps: begin_step must really restart from zero
+        fg.begin_step()
+        for i in pkg.shard_views(n_views, rank, world):
+            _loss(params, views[i]).backward()
+        fg.allreduce(n_views)
+        assert all(p.grad.data_ptr() == v.data_ptr() for p, v in zip(params, fg.views))
+        grads.append([p.grad.clone() for p in params])
+    out[rank] = grads
+    dist.destroy_process_group()
+
+
+def test_flat_gradients_one_collective_equals_single_process_mean():
+    world, n_views = 2, 5
+    port = 29000 + (os.getpid() % 500)
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker_flat, args=(world, port, n_views, out), nprocs=world, join=True)
+    torch.manual_seed(1)
+    params = [torch.randn(7, 3, requires_grad=True), torch.randn(5, requires_grad=True)]
+    (sum(_loss(params, v) for v in _views(n_views)) / n_views).backward()
+    for r in range(world):
+        for step in range(2):
+            for g, p in zip(out[r][step], params):
+                torch.testing.assert_close(g, p.grad, rtol=1e-5, atol=1e-6)

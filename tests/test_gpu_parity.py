@@ -208,10 +208,11 @@ def test_two_level_binning_edge_cases(pkg, oracle, W, H):
     for sel in (slice(None), slice(0, 1), slice(3, 4)):
         args = [t[sel].contiguous() for t in dev_args]
         ref = pkg.project_and_bin(*args, 3, cam, W, H, method="keys64")
-        got = pkg.project_and_bin(*args, 3, cam, W, H, method="coarse", with_isect_ids=True)
-        assert got["M"] == ref["M"]
-        assert torch.equal(got["flatten_ids"], ref["flatten_ids"]) and torch.equal(got["isect_offsets"], ref["isect_offsets"])
-        assert torch.equal(got["isect_ids"], ref["isect_ids"])
+        for method in ("coarse", "coarse-gather"):  # rectangles packed by the projection kernel / recomputed in b200_bin_coarse
+            got = pkg.project_and_bin(*args, 3, cam, W, H, method=method, with_isect_ids=True)
+            assert got["M"] == ref["M"]
+            assert torch.equal(got["flatten_ids"], ref["flatten_ids"]) and torch.equal(got["isect_offsets"], ref["isect_offsets"])
+            assert torch.equal(got["isect_ids"], ref["isect_ids"])
     # nothing visible: M = 0
     far = dev_args[0].clone()
     far[:, 2] = -1.0

@@ -127,3 +127,23 @@ def test_store_lazy_zero_grad_equals_eager(pkg, oracle, deg):
     st._flat_grad.fill_(5.0)
     st.zero_grad(lazy=True)
     assert st.flat_grad.abs().max().item() == 0.0  # no backward ran: the property performs the postponed memset
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_second_device_in_the_same_process(pkg, oracle):
+    """kernel attributes (dynamic shared memory above 48 KB: bulk SH staging, tile_prep / tile_count grids, the
+    onesweep passes) are per DEVICE; a process that rendered on cuda:0 must be able to render on cuda:1 afterwards."""
+    N, W, H = 6000, 640, 360
+    sc = oracle.synthetic_scene(N, W, H, seed=3)
+    act = oracle.activate(sc)
+    outs = []
+    for d in ("cuda:0", "cuda:1", "cuda:0"):
+        leaves = {k: act[k].to(d).clone().requires_grad_(True) for k in act}
+        be = pkg.B200Backend(sc["K"].to(d))
+        vp = {"world_view_transform": sc["viewmat"].to(d), "image_width": W, "image_height": H}
+        res = be.render_with_depth(leaves, vp, bg_color=torch.zeros(3, device=d), render_mode="RGB", device=d, sh_degree=3)
+        res["render"].sum().backward()
+        torch.cuda.synchronize(d)
+        outs.append((res["render"].detach().cpu(), leaves["means3D"].grad.cpu()))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][0], outs[2][0])
+    assert torch.allclose(outs[0][1], outs[1][1], rtol=1e-4, atol=1e-6)
