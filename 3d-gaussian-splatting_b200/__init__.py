@@ -14,9 +14,9 @@ from .loss import l1_ssim_loss  # noqa: F401
 from .optim import StoreAdam  # noqa: F401
 from .streams import ViewStreams  # noqa: F401
 from . import dropin  # noqa: F401
-from .distributed import FlatGradients, balance_views, shard_views, allreduce_gradients, allreduce_flat, ViewShardedStep  # noqa: F401
+from .distributed import FlatGradients, SymmetricBuffer, balance_views, shard_views, allreduce_gradients, allreduce_flat, ViewShardedStep  # noqa: F401
 
 __all__ = [
     "rasterization", "project_and_bin", "RasterizeSplats", "make_cam", "B200Backend", "densify_stats", "GaussianStore", "l1_ssim_loss", "StoreAdam",
-    "ViewStreams", "FlatGradients", "balance_views", "shard_views", "allreduce_gradients", "allreduce_flat", "ViewShardedStep",
+    "ViewStreams", "FlatGradients", "SymmetricBuffer", "balance_views", "shard_views", "allreduce_gradients", "allreduce_flat", "ViewShardedStep",
 ]

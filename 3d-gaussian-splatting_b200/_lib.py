@@ -61,6 +61,11 @@ SIGNATURES = {
     "b200_adam_step_stats": (_i, [_p, _p, _p, _p, _l, _p, _i, _i, C.c_float, C.c_float, C.c_float, _p, _l, _p, _p, _p]),
     "b200_store_gather": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _l, _p]),
     "b200_densify_stats": (_i, [_p, _l, _p, _p, _p]),
+    "b200_allreduce_multimem": (_i, [_p, _l, _i, _i, C.c_float, _i, _p]),
+    "b200_multimem_slice": (None, [_l, _i, _i, _p, _p]),
+    "b200_allreduce_adam_multimem": (_i, [_p, _p, _p, _p, _p, _l, _i, _i, C.c_float, _p, _i, _i, C.c_float, C.c_float, C.c_float,
+                                          _l, _l, _i, _p]),
+    "b200_share_slice_multimem": (_i, [_p, _p, _l, _i, _i, _p]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

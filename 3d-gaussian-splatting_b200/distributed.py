@@ -72,16 +72,51 @@ def allreduce_gradients(params: Iterable[torch.Tensor], n_global_views: int, gro
     return None
 
 
+class SymmetricBuffer:
+    """A flat fp32 buffer replicated in SYMMETRIC memory on every rank of ``group`` (one multicast address range over
+    NVSwitch) whose sum-all-reduce is this library's own kernel (``b200_allreduce_multimem``: ``multimem.ld_reduce`` /
+    ``multimem.st``, csrc/collective.cu) instead of an NCCL call.  Allocation, rendezvous and the cross-rank barriers are
+    host plumbing from ``torch.distributed._symmetric_memory``; construction is collective (every rank, same ``numel``).
+    Raises if the fabric has no multicast support — there is no silent fall-back; callers choose NCCL explicitly."""
+
+    def __init__(self, numel: int, device, group=None, max_ctas: int = 0):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.group = group if group is not None else dist.group.WORLD
+        n = (int(numel) + 3) // 4 * 4
+        self.tensor = symm_mem.empty(n, dtype=torch.float32, device=device)
+        self.handle = symm_mem.rendezvous(self.tensor, self.group)
+        self.mc_ptr = int(self.handle.multicast_ptr)
+        if self.mc_ptr == 0:
+            raise RuntimeError("SymmetricBuffer: no multicast (NVLink SHARP) support on this fabric")
+        self.rank, self.world, self.max_ctas = dist.get_rank(self.group), dist.get_world_size(self.group), int(max_ctas)
+        self.tensor.zero_()
+
+    def allreduce_(self, scale: float = 1.0) -> torch.Tensor:
+        """tensor <- scale * sum over ranks, on every rank (bit-identical replicas), on the current stream."""
+        from ._lib import lib, check
+        t = self.tensor
+        with torch.cuda.device(t.device):
+            self.handle.barrier(channel=0)  # every rank's backward has finished writing its replica
+            check(lib.b200_allreduce_multimem(self.mc_ptr, t.numel(), self.rank, self.world, float(scale), self.max_ctas,
+                                              torch.cuda.current_stream().cuda_stream), "b200_allreduce_multimem")
+            self.handle.barrier(channel=1)  # every slice is stored before anyone reads its replica
+        return t
+
+
 class FlatGradients:
     """The parameters' ``.grad`` as views of ONE flat buffer (what DDP calls ``gradient_as_bucket_view``), for the drop-in
     path, whose five gradient tensors autograd otherwise allocates separately: ``begin_step()`` zeroes the buffer and
     re-attaches the views, autograd accumulates every view's gradients into them in place, ``allreduce(n_views)`` is then
     ONE collective instead of five back-to-back ones (three of which — 4 to 16 MB — are latency-bound at 8 ranks)."""
 
-    def __init__(self, params: Sequence[torch.Tensor]):
+    def __init__(self, params: Sequence[torch.Tensor], symmetric: bool = False, group=None):
+        """symmetric=True: the buffer lives in symmetric memory and is reduced by this library's multimem kernel
+        (:class:`SymmetricBuffer`) instead of NCCL — collective construction."""
         self.params = [p for p in params if p.requires_grad]
         sizes = [(p.numel() + 3) // 4 * 4 for p in self.params]  # 16-byte aligned slices
-        self.flat = torch.zeros(sum(sizes), dtype=self.params[0].dtype, device=self.params[0].device)
+        self.sym = SymmetricBuffer(sum(sizes), self.params[0].device, group) if symmetric else None
+        self.flat = self.sym.tensor if symmetric else torch.zeros(sum(sizes), dtype=self.params[0].dtype,
+                                                                   device=self.params[0].device)
         self.views, o = [], 0
         for p, n in zip(self.params, sizes):
             self.views.append(self.flat[o: o + p.numel()].view_as(p))
@@ -96,6 +131,8 @@ class FlatGradients:
         for p, v in zip(self.params, self.views):
             if p.grad is None or p.grad.data_ptr() != v.data_ptr():
                 raise RuntimeError("FlatGradients: a .grad was replaced since begin_step() (zero_grad(set_to_none=True)?)")
+        if self.sym is not None:
+            return self.sym.allreduce_(1.0 / float(n_global_views))
         return allreduce_flat(self.flat, 1.0 / float(n_global_views), group)
 
 

@@ -65,8 +65,19 @@ class GaussianStore(nn.Module):
         # bumped on every (re-)allocation: whoever holds buffers laid out like `flat` (StoreAdam's moments, ViewStreams'
         # accumulator nodes, optimisers built from optimizer_groups) can tell that the population changed under them
         self.generation = getattr(self, "generation", -1) + 1
-        self.flat = torch.zeros(o, dtype=torch.float32, device=dev)
-        self._flat_grad = torch.zeros(o, dtype=torch.float32, device=dev)
+        group = getattr(self, "_sym_group", None)
+        if group is None:
+            self._sym_flat = self._sym_grad = None
+            self.flat = torch.zeros(o, dtype=torch.float32, device=dev)
+            self._flat_grad = torch.zeros(o, dtype=torch.float32, device=dev)
+        else:
+            # parameters and gradients replicated in SYMMETRIC memory (one multicast range over NVSwitch): the gradient
+            # all-reduce / the fused reduce-scatter + Adam + all-gather are this library's multimem kernels
+            # (distributed.SymmetricBuffer, csrc/collective.cu).  Collective: every rank allocates the same size.
+            from .distributed import SymmetricBuffer
+            self._sym_flat = SymmetricBuffer(o, dev, group)
+            self._sym_grad = SymmetricBuffer(o, dev, group)
+            self.flat, self._flat_grad = self._sym_flat.tensor, self._sym_grad.tensor
         # shared with the backward pass (rasterization.RasterizeSplats): True after zero_grad(lazy=True) until the first
         # backward has WRITTEN the buffer instead of adding into it
         self._grad_state = {"pending_zero": False}
@@ -110,6 +121,30 @@ class GaussianStore(nn.Module):
 
     def __len__(self) -> int:
         return self._n
+
+    @torch.no_grad()
+    def make_symmetric(self, group=None) -> "GaussianStore":
+        """Move the flat parameter and gradient buffers into symmetric (multicast) memory shared with the ranks of
+        ``group`` — collective, every rank with the same population.  Afterwards ``allreduce_grads`` and
+        ``StoreAdam(sharded=True)`` use this library's multimem kernels instead of NCCL; ``densify_and_prune`` re-allocates
+        symmetrically (call it on every rank, as the replicated training loop does anyway).  The ``Parameter`` objects are
+        re-created (``generation`` is bumped)."""
+        import torch.distributed as dist
+        old = self.flat
+        self._sym_group = group if group is not None else dist.group.WORLD
+        stats = (self.xyz_gradient_accum, self.xyz_gradient_count, self.max_radii_2D)
+        self._allocate(self._n, old.device)
+        self.flat.copy_(old)
+        self.xyz_gradient_accum, self.xyz_gradient_count, self.max_radii_2D = stats
+        return self
+
+    def allreduce_grads(self, scale: float) -> torch.Tensor:
+        """flat_grad <- scale * sum over ranks: the library's multimem kernel when the store is symmetric, NCCL otherwise."""
+        from .distributed import allreduce_flat
+        g = self.flat_grad  # (resolves a pending lazy zero)
+        if self._sym_grad is not None:
+            return self._sym_grad.allreduce_(scale)
+        return allreduce_flat(g, scale)
 
     # ------------------------------------------------------------------ reference getters (gaussian_model.py:90-108)
     @property
@@ -247,10 +282,13 @@ class GaussianStore(nn.Module):
         n_new = int(src_rows.numel())
         m_old = v_old = None
         if optimizer is not None:
+            if getattr(optimizer, "sharded", False):
+                optimizer.gather_moments()  # every rank holds only its slice of the moments: complete them first
             m_old, v_old = optimizer.exp_avg, optimizer.exp_avg_sq
         self._allocate(n_new, dev)  # fresh flat / flat_grad, parameters re-created as views
-        m_new = torch.zeros_like(self.flat) if optimizer is not None else None
-        v_new = torch.zeros_like(self.flat) if optimizer is not None else None
+        new_moment = getattr(optimizer, "_new_moment", None) or (lambda flat: torch.zeros_like(flat))
+        m_new = new_moment(self.flat) if optimizer is not None else None
+        v_new = new_moment(self.flat) if optimizer is not None else None
         src_rows = src_rows.to(torch.int64).contiguous()
         ks = keep_state.to(torch.uint8).contiguous()
         ptr = lambda t: None if t is None else t.data_ptr()  # noqa: E731

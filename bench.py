@@ -293,7 +293,15 @@ def run_b200(args):
     # N > 1: the five gradient tensors are views of ONE flat buffer (distributed.FlatGradients), reduced by one collective
     # (opt-in: measured at N=2 it costs more — the memset and the first view's in-place add, 0.2 ms — than the one collective
     # saves, 0.12 ms: 5.42 -> 5.56 ms per step)
-    flat_grads = pkg.FlatGradients(params_list) if (world > 1 and args.flat_grads) else None
+    # --flat-grads sym: the flat buffer in symmetric memory, reduced by the library's multimem kernel (0.55 ms against NCCL's
+    # 0.64 ms for one / 0.93 ms for five collectives at 8 ranks; slower than NCCL at 2 ranks) — the default from 8 ranks on
+    fg_mode = args.flat_grads or ("sym" if world >= 8 else "off")
+    flat_grads = None
+    if world > 1 and fg_mode != "off":
+        try:
+            flat_grads = pkg.FlatGradients(params_list, symmetric=(fg_mode == "sym"))
+        except Exception as e:  # no multicast on this fabric: stay on NCCL's five collectives, and say so
+            fg_mode = f"off (symmetric memory unavailable: {type(e).__name__})"
 
     def step_device(step):
         """inputs resident in HBM: pose + cotangent on device."""
@@ -404,8 +412,21 @@ def run_b200(args):
     # trainer.py:854-859 caps the log-scales every iteration at log(scene_extent * scale_clamp_ratio): folded into Adam
     adam = pkg.StoreAdam(store, ref_lrs, scale_ceiling=math.log(10.0 * 0.2 + 1e-9))
     train_state = {"k": 0, "primed": False}
+    # N > 1: the optimiser of the train leg is the fused multimem kernel (gradient reduce-scatter + Adam on the rank's slice +
+    # parameter all-gather, sharded moments) on a store in symmetric memory — when the fabric has multicast; else NCCL + Adam
+    train_store, train_adam, train_mode = store, adam, ("single GPU" if world == 1 else "NCCL all-reduce + Adam on every rank")
+    if world > 1 and not args.no_fused_optimizer:
+        try:
+            train_store = pkg.GaussianStore.from_tensors(sc["xyz"].to(dev), sc["features_dc"].to(dev), sc["features_rest"].to(dev),
+                                                         sc["scaling"].to(dev), sc["rotation"].to(dev), sc["opacity"].to(dev)).make_symmetric()
+            train_adam = pkg.StoreAdam(train_store, ref_lrs, scale_ceiling=math.log(10.0 * 0.2 + 1e-9), sharded=True)
+            train_mode = "fused multimem kernel: reduce-scatter + Adam on the rank's slice + parameter all-gather (csrc/collective.cu)"
+        except Exception as e:
+            train_store, train_adam = store, adam
+            train_mode += f" (symmetric memory unavailable: {type(e).__name__})"
 
     def step_train(step):
+        store = train_store
         store.zero_grad(lazy=True)  # the first backward writes the flat gradient buffer (no memset, no read-modify-write)
         losses = []
         vstreams.begin()
@@ -431,8 +452,9 @@ def run_b200(args):
                 train_state["k"] = k + 1
         vstreams.join()
         if world > 1:
-            pkg.allreduce_flat(store.flat_grad, 1.0 / world)
-        adam.step(densify_stats=True)  # K10 rides in the optimiser pass (adam.cu)
+            train_adam.step_allreduce(1.0 / world, densify_stats=True)  # fused (sharded) or NCCL + Adam, see train_mode
+        else:
+            train_adam.step(densify_stats=True)  # K10 rides in the optimiser pass (adam.cu)
         return float(torch.stack(losses).sum().item())
 
     def timed(fn, steps, warmup, timer=None):
@@ -633,8 +655,10 @@ def run_b200(args):
         "reference_trainer_it_per_s": (ref_trainer or {}).get("it_per_s"),
         "reference_trainer": ref_trainer,
         "multi_gpu": multi_gpu,
-        "gradient_collective": (None if world == 1 else ("five all-reduces back to back (one per attribute tensor)" if not args.flat_grads else
-                                "ONE all-reduce: the five .grad tensors are views of a flat buffer (FlatGradients)")),
+        "gradient_collective": (None if world == 1 else {"off": "five NCCL all-reduces back to back (one per attribute tensor)",
+                                                         "nccl": "ONE NCCL all-reduce of a flat buffer the five .grad tensors are views of",
+                                                         "sym": "ONE all-reduce by this library's multimem kernel (csrc/collective.cu) over a flat "
+                                                                "gradient buffer in symmetric memory"}.get(fg_mode, fg_mode)),
         "view_assignment": ("one rank" if world == 1 else ("plain order" if args.no_balance else
                             "balance_views: the step's N*V cameras dealt to the ranks by intersection count M (LPT)")),
         "oracle_pin": gsplat_probe(),
@@ -651,6 +675,7 @@ def run_b200(args):
                                   "accumulation into the flat buffer); not the drop-in call, reported beside it"},
         "train_step": {"it_per_s": 1e3 / (ms_train / args.steps), "ms_per_step": ms_train / args.steps,
                        "Mpix_per_s": pix_per_step / (ms_train / args.steps / 1e3) / 1e6, "views_per_step": world * V,
+                       "optimizer": train_mode,
                        "what": "full optimiser iteration on the widened path (SURVEY §8 f1+f3+f4): host pose+GT upload, "
                                "GaussianStore.render, fused L1+SSIM loss, backward, all-reduce if N>1, one-kernel Adam, "
                                "densification statistic, loss read back"},
@@ -674,9 +699,12 @@ def main():
     ap.add_argument("--views-per-rank", type=int, default=4)
     ap.add_argument("--view-streams", type=int, default=2,
                     help="CUDA streams the views of a step alternate over (ViewStreams); 1 = one stream")
-    ap.add_argument("--flat-grads", action="store_true",
-                    help="N>1, drop-in path: make the five .grad tensors views of one flat buffer and reduce it with ONE collective "
-                         "(default: autograd allocates them, five collectives back to back)")
+    ap.add_argument("--flat-grads", default="", choices=["", "off", "nccl", "sym"],
+                    help="N>1, drop-in path: 'off' = autograd allocates the five .grad tensors, five NCCL collectives back to back; "
+                         "'nccl' = views of one flat buffer, ONE NCCL collective; 'sym' = the flat buffer in symmetric memory, reduced by "
+                         "the library's multimem kernel.  Default: 'sym' from 8 ranks on, else 'off'")
+    ap.add_argument("--no-fused-optimizer", action="store_true",
+                    help="N>1, train leg: NCCL all-reduce + Adam on every rank instead of the fused multimem optimiser kernel")
     ap.add_argument("--no-balance", action="store_true",
                     help="N>1: deal the cameras of a step to the ranks in plain order instead of balancing them by M")
     ap.add_argument("--no-reference-trainer", action="store_true",

@@ -283,6 +283,31 @@ int b200_store_gather(const float* params_src, const float* exp_avg_src, const f
                       float* exp_avg_sq_dst, const int64_t* layout_dst_host, const int64_t* src_row,
                       const uint8_t* keep_state, int64_t n_dst, void* stream);
 
+/* ---- multi-GPU: the gradient all-reduce as this library's kernel over NVSwitch multicast memory -----------------------
+ * The reference has no distributed code; BASELINE.json north_star asks for the parameter gradients to be
+ * reduced over NVLink.  mc_ptr is the MULTICAST address of a flat fp32 buffer replicated in symmetric memory on all
+ * `world` ranks (host plumbing: torch.distributed._symmetric_memory).  Rank `rank` reads its 1/world slice once with
+ * multimem.ld_reduce.add.v4.f32 (the switch sums the replicas), scales it and writes it to every replica with
+ * multimem.st.v4.f32.  In place; n_floats % 4 == 0; the caller brackets the call with cross-rank barriers on the same
+ * stream.  max_ctas <= 0: 148. */
+int b200_allreduce_multimem(float* mc_ptr, int64_t n_floats, int rank, int world, float scale, int max_ctas, void* stream);
+/* The slice [begin, end) (floats, multiples of 4) of an n_floats buffer that rank `rank` of `world` reduces / updates. */
+void b200_multimem_slice(int64_t n_floats, int rank, int world, int64_t* begin_float, int64_t* end_float);
+/* Reduce-scatter of the gradient + Adam on the rank's slice + all-gather of the PARAMETERS in one kernel (the optimiser of
+ * trainer.py:331-340,505-511 for the view-sharded step): for every 16-byte vector of this rank's slice the switch-summed
+ * gradient (multimem.ld_reduce over mc_grads, times grad_scale) drives b200_adam_step's arithmetic on the LOCAL parameter
+ * and moments (`params` = this rank's replica, exp_avg / exp_avg_sq: only the slice is touched — sharded moments), and the
+ * updated parameter is written to every replica (multimem.st over mc_params).  Inside [keep_grad_begin, keep_grad_end)
+ * (the position block) the reduced gradient is also written to every replica of the gradient buffer, so that the
+ * densification statistic (trainer.py:786-791) can be taken locally afterwards.  seg_host as b200_adam_step.  The caller
+ * brackets the call with cross-rank barriers. */
+int b200_allreduce_adam_multimem(float* mc_grads, float* mc_params, const float* params, float* exp_avg,
+                                 float* exp_avg_sq, int64_t n_floats, int rank, int world, float grad_scale,
+                                 const double* seg_host, int n_seg, int step, float beta1, float beta2, float eps,
+                                 int64_t keep_grad_begin, int64_t keep_grad_end, int max_ctas, void* stream);
+/* Every replica of this rank's slice of the symmetric buffer <- the rank's local copy. */
+int b200_share_slice_multimem(float* mc_ptr, const float* local, int64_t n_floats, int rank, int world, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
