@@ -295,13 +295,26 @@ def run_b200(args):
     # saves, 0.12 ms: 5.42 -> 5.56 ms per step)
     # --flat-grads sym: the flat buffer in symmetric memory, reduced by the library's multimem kernel (0.55 ms against NCCL's
     # 0.64 ms for one / 0.93 ms for five collectives at 8 ranks; slower than NCCL at 2 ranks) — the default from 8 ranks on
-    fg_mode = args.flat_grads or ("sym" if world >= 8 else "off")
-    flat_grads = None
-    if world > 1 and fg_mode != "off":
-        try:
-            flat_grads = pkg.FlatGradients(params_list, symmetric=(fg_mode == "sym"))
-        except Exception as e:  # no multicast on this fabric: stay on NCCL's five collectives, and say so
-            fg_mode = f"off (symmetric memory unavailable: {type(e).__name__})"
+    # Measured at 8 ranks (profiles/r02/bench_A_n8*.json): the e2e leg (host read-back every step) gains the collective's
+    # 0.33 ms (7.12 -> 6.78 ms); the device leg, whose host runs ahead with the views on two streams, loses 0.17 ms
+    # (5.78 -> 5.95 ms: the flat buffer's memset and the extra in-place add of the first view land on the caller's stream,
+    # between the views).  Defaults therefore: device leg 'off' at every N, e2e leg 'sym' from 8 ranks on.
+    fg_mode = args.flat_grads or "off"
+    fg_mode_e2e = args.flat_grads or ("sym" if world >= 8 else "off")
+    flat_by_mode = {}
+
+    def make_flat(mode):
+        if world == 1 or mode == "off":
+            return None, mode
+        if mode not in flat_by_mode:
+            try:
+                flat_by_mode[mode] = pkg.FlatGradients(params_list, symmetric=(mode == "sym"))
+            except Exception as e:  # no multicast on this fabric: stay on NCCL's five collectives, and say so
+                return None, f"off (symmetric memory unavailable: {type(e).__name__})"
+        return flat_by_mode[mode], mode
+
+    flat_grads, fg_mode = make_flat(fg_mode)
+    flat_grads_e2e, fg_mode_e2e = make_flat(fg_mode_e2e)
 
     def step_device(step):
         """inputs resident in HBM: pose + cotangent on device."""
@@ -353,8 +366,8 @@ def run_b200(args):
         """through the public backend call with HOST buffers: pose + ground-truth frame uploaded from pinned
         memory every view, L1 + D-SSIM loss, backward, loss read back (what trainer.py:270-281,485-497 does per view)."""
         nonlocal flat
-        if flat_grads is not None:
-            flat_grads.begin_step()
+        if flat_grads_e2e is not None:
+            flat_grads_e2e.begin_step()
         else:
             for p in params_list:
                 p.grad = None
@@ -382,8 +395,8 @@ def run_b200(args):
                 losses.append(loss.detach())
                 e2e_state["k"] = k + 1
         vstreams.join()
-        if flat_grads is not None:
-            flat_grads.allreduce(world * V)
+        if flat_grads_e2e is not None:
+            flat_grads_e2e.allreduce(world * V)
         elif world > 1:
             flat = pkg.allreduce_gradients(params_list, world * V, flat=flat)
         return float(torch.stack(losses).sum().item())  # D2H read of the step's result
@@ -655,10 +668,11 @@ def run_b200(args):
         "reference_trainer_it_per_s": (ref_trainer or {}).get("it_per_s"),
         "reference_trainer": ref_trainer,
         "multi_gpu": multi_gpu,
-        "gradient_collective": (None if world == 1 else {"off": "five NCCL all-reduces back to back (one per attribute tensor)",
-                                                         "nccl": "ONE NCCL all-reduce of a flat buffer the five .grad tensors are views of",
-                                                         "sym": "ONE all-reduce by this library's multimem kernel (csrc/collective.cu) over a flat "
-                                                                "gradient buffer in symmetric memory"}.get(fg_mode, fg_mode)),
+        "gradient_collective": (None if world == 1 else {leg: {
+            "off": "five NCCL all-reduces back to back (one per attribute tensor)",
+            "nccl": "ONE NCCL all-reduce of a flat buffer the five .grad tensors are views of",
+            "sym": "ONE all-reduce by this library's multimem kernel (csrc/collective.cu) over a flat gradient buffer in symmetric memory",
+        }.get(m, m) for leg, m in (("value", fg_mode), ("e2e", fg_mode_e2e))}),
         "view_assignment": ("one rank" if world == 1 else ("plain order" if args.no_balance else
                             "balance_views: the step's N*V cameras dealt to the ranks by intersection count M (LPT)")),
         "oracle_pin": gsplat_probe(),

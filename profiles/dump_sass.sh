@@ -38,3 +38,5 @@ dump api.o 'densify_stats_kernel' densify_stats.sass
 dump adam.o 'adam_kernel' adam.sass
 dump loss.o 'l1_ssim' l1_ssim.sass
 dump densify.o 'store_gather' store_gather.sass
+# multi-GPU: the library's own collectives over NVSwitch multicast memory
+dump collective.o 'multimem_allreduce_kernelILi4|multimem_adam_kernel|multimem_share_slice' collective_multimem.sass
