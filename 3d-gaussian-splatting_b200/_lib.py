@@ -11,7 +11,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200splat.so")
+LIB_PATH = os.environ.get("B200_LIB") or os.path.join(_HERE, "libb200splat.so")  # B200_LIB: a tuning build of the same ABI
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(

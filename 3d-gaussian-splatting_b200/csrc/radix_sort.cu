@@ -15,7 +15,9 @@
 #define RS_RADIX 256
 #define RS_THREADS 256
 #define RS_WARPS (RS_THREADS / 32)
+#ifndef RS_ITEMS
 #define RS_ITEMS 16
+#endif
 #define RS_TILE (RS_THREADS * RS_ITEMS)
 #define RS_MAX_PASSES 8
 #define RS_LOOKBACK 8  // predecessor status words fetched per look-back step (memory-level parallelism)
