@@ -103,6 +103,51 @@ class SymmetricBuffer:
         return t
 
 
+class GradientArena:
+    """Drop-in path, N GPUs: make autograd's own `.grad` tensors live inside ONE flat buffer in symmetric memory WITHOUT the
+    bookkeeping cost of :class:`FlatGradients` (no memset, no extra in-place add of the first view).
+
+    The rasterizer's backward writes every row of its five gradient outputs (zeros for culled Gaussians included).  Once per
+    step — for whichever view's backward runs first — ``take`` hands it slices of the arena as those outputs; autograd adopts
+    a fresh, contiguous incoming gradient of a leaf as its ``.grad`` without copying, and accumulates the later views into it
+    in place.  ``allreduce`` then checks that every ``p.grad`` really is the arena's slice (it is not if the inputs were not
+    leaves, or a hook cloned the gradient) and reduces the whole buffer with ONE multimem kernel; anything that did not land
+    in the arena falls back to NCCL.  Activate with ``rasterization.set_gradient_arena(arena)``."""
+
+    def __init__(self, like: Sequence[torch.Tensor], group=None):
+        """like: tensors with the shapes of (means, quats, scales, opacities, colors) — e.g. the five leaves themselves."""
+        self.shapes = [tuple(t.shape) for t in like]
+        sizes = [(t.numel() + 3) // 4 * 4 for t in like]
+        self.sym = SymmetricBuffer(sum(sizes), like[0].device, group)
+        self.views, self._spans, o = [], [], 0
+        for t, n in zip(like, sizes):
+            self.views.append(self.sym.tensor[o: o + t.numel()].view(t.shape))
+            self._spans.append((o, t.numel(), tuple(t.shape)))
+            o += n
+        self._available = False
+
+    def begin_step(self) -> None:
+        self._available = True
+
+    def take(self, inputs: Sequence[torch.Tensor]):
+        if not self._available or [tuple(t.shape) for t in inputs] != self.shapes or inputs[0].device != self.sym.tensor.device:
+            return None
+        self._available = False
+        # FRESH view objects: autograd adopts an incoming gradient as .grad without a copy only if nothing else references
+        # that tensor object (AccumulateGrad's use-count test), so the arena's own `views` must not be what is handed out
+        return tuple(self.sym.tensor[o: o + n].view(shape) for o, n, shape in self._spans)
+
+    def allreduce(self, params: Sequence[torch.Tensor], n_global_views: int, group=None) -> bool:
+        """params in the order (means, quats, scales, opacities, colors).  True if the own collective was used."""
+        inside = all(p.grad is not None and p.grad.data_ptr() == v.data_ptr() and p.grad.is_contiguous()
+                     for p, v in zip(params, self.views))
+        if inside:
+            self.sym.allreduce_(1.0 / float(n_global_views))
+            return True
+        allreduce_gradients(list(params), n_global_views, group)
+        return False
+
+
 class FlatGradients:
     """The parameters' ``.grad`` as views of ONE flat buffer (what DDP calls ``gradient_as_bucket_view``), for the drop-in
     path, whose five gradient tensors autograd otherwise allocates separately: ``begin_step()`` zeroes the buffer and

@@ -326,6 +326,17 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
     return out
 
 
+# Optional provider of the gradient tensors the (non-accumulating) backward returns: distributed.GradientArena hands out, once
+# per step, views of ONE flat buffer in symmetric memory, so that autograd's `.grad` tensors end up inside it without a copy
+# and the multi-GPU all-reduce is a single multimem kernel (set with set_gradient_arena; None = torch.empty_like).
+_GRAD_ARENA = None
+
+
+def set_gradient_arena(arena) -> None:
+    global _GRAD_ARENA
+    _GRAD_ARENA = arena
+
+
 _ACC_EVENTS = {}  # (device, gradient-buffer address) -> event after the last in-place accumulation into it
 
 
@@ -413,11 +424,15 @@ class RasterizeSplats(torch.autograd.Function):
                     if gbuf.numel() != ref.numel() or not gbuf.is_contiguous() or gbuf.dtype != torch.float32:
                         raise RuntimeError("grad_into buffers must be contiguous fp32 with the parameters' sizes")
             else:
-                v_means = torch.empty_like(means)
-                v_quats = torch.empty_like(quats)
-                v_scales = torch.empty_like(scales)
-                v_opac = torch.empty_like(opacities)
-                v_colors = torch.empty_like(colors)
+                bufs = _GRAD_ARENA.take((means, quats, scales, opacities, colors)) if _GRAD_ARENA is not None else None
+                if bufs is not None:  # first backward of the step: its outputs ARE the arena's slices (autograd adopts them as .grad)
+                    v_means, v_quats, v_scales, v_opac, v_colors = bufs
+                else:
+                    v_means = torch.empty_like(means)
+                    v_quats = torch.empty_like(quats)
+                    v_scales = torch.empty_like(scales)
+                    v_opac = torch.empty_like(opacities)
+                    v_colors = torch.empty_like(colors)
             acc_key = None
             if grad_into is not None:
                 # the in-place "+=" of the accumulate mode is not atomic: views in flight on different streams

@@ -295,20 +295,41 @@ def run_b200(args):
     # saves, 0.12 ms: 5.42 -> 5.56 ms per step)
     # --flat-grads sym: the flat buffer in symmetric memory, reduced by the library's multimem kernel (0.55 ms against NCCL's
     # 0.64 ms for one / 0.93 ms for five collectives at 8 ranks; slower than NCCL at 2 ranks) — the default from 8 ranks on
-    # Measured at 8 ranks (profiles/r02/bench_A_n8*.json): the e2e leg (host read-back every step) gains the collective's
-    # 0.33 ms (7.12 -> 6.78 ms); the device leg, whose host runs ahead with the views on two streams, loses 0.17 ms
-    # (5.78 -> 5.95 ms: the flat buffer's memset and the extra in-place add of the first view land on the caller's stream,
-    # between the views).  Defaults therefore: device leg 'off' at every N, e2e leg 'sym' from 8 ranks on.
-    fg_mode = args.flat_grads or "off"
-    fg_mode_e2e = args.flat_grads or ("sym" if world >= 8 else "off")
+    # Measured (profiles/r02/bench_A_n*_{arena,off}.json): 'sym' / 'nccl' pay a memset and an extra in-place add of the first
+    # view per step (FlatGradients), which costs the device leg more than the single collective saves; 'arena' has neither and
+    # wins from 4 ranks on — value leg 5.63 -> 5.57 ms at 4 ranks, 5.73 -> 5.47 ms at 8; e2e leg 6.40 -> 6.25 and 7.18 -> 6.79 ms
+    # — and loses at 2 (5.40 -> 5.55 ms: with two members the switch round trip of multimem buys nothing).
+    # 'arena' (distributed.GradientArena) gets the same single own collective WITHOUT that bookkeeping: the first backward of a
+    # step writes its gradients straight into slices of the symmetric buffer and autograd adopts them as .grad.
+    default_mode = "arena" if world >= 4 else "off"
+    fg_mode = args.flat_grads or default_mode
+    fg_mode_e2e = args.flat_grads or default_mode
     flat_by_mode = {}
+    arena_params = [leaves["means3D"], leaves["rotations"], leaves["scales"], leaves["opacities"], leaves["shs"]]
+
+    class _Arena:  # FlatGradients' two-call interface over GradientArena
+        def __init__(self):
+            self.arena = pkg.GradientArena([leaves["means3D"], leaves["rotations"], leaves["scales"],
+                                            leaves["opacities"].squeeze(-1), leaves["shs"]])
+            self.hits = self.steps = 0
+
+        def begin_step(self):
+            for p in params_list:
+                p.grad = None
+            pkg.set_gradient_arena(self.arena)
+            self.arena.begin_step()
+
+        def allreduce(self, n_views):
+            self.hits += int(self.arena.allreduce(arena_params, n_views))
+            self.steps += 1
+            pkg.set_gradient_arena(None)
 
     def make_flat(mode):
         if world == 1 or mode == "off":
             return None, mode
         if mode not in flat_by_mode:
             try:
-                flat_by_mode[mode] = pkg.FlatGradients(params_list, symmetric=(mode == "sym"))
+                flat_by_mode[mode] = _Arena() if mode == "arena" else pkg.FlatGradients(params_list, symmetric=(mode == "sym"))
             except Exception as e:  # no multicast on this fabric: stay on NCCL's five collectives, and say so
                 return None, f"off (symmetric memory unavailable: {type(e).__name__})"
         return flat_by_mode[mode], mode
@@ -672,7 +693,11 @@ def run_b200(args):
             "off": "five NCCL all-reduces back to back (one per attribute tensor)",
             "nccl": "ONE NCCL all-reduce of a flat buffer the five .grad tensors are views of",
             "sym": "ONE all-reduce by this library's multimem kernel (csrc/collective.cu) over a flat gradient buffer in symmetric memory",
+            "arena": "ONE all-reduce by this library's multimem kernel (csrc/collective.cu): autograd's .grad tensors are slices of a "
+                     "symmetric buffer handed to the first backward of the step (GradientArena)",
         }.get(m, m) for leg, m in (("value", fg_mode), ("e2e", fg_mode_e2e))}),
+        "gradient_arena_hits": ({m: f"{o.hits}/{o.steps} steps reduced by the own collective" for m, o in flat_by_mode.items()
+                                if isinstance(o, _Arena)} or None),
         "view_assignment": ("one rank" if world == 1 else ("plain order" if args.no_balance else
                             "balance_views: the step's N*V cameras dealt to the ranks by intersection count M (LPT)")),
         "oracle_pin": gsplat_probe(),
@@ -713,10 +738,12 @@ def main():
     ap.add_argument("--views-per-rank", type=int, default=4)
     ap.add_argument("--view-streams", type=int, default=2,
                     help="CUDA streams the views of a step alternate over (ViewStreams); 1 = one stream")
-    ap.add_argument("--flat-grads", default="", choices=["", "off", "nccl", "sym"],
+    ap.add_argument("--flat-grads", default="", choices=["", "off", "nccl", "sym", "arena"],
                     help="N>1, drop-in path: 'off' = autograd allocates the five .grad tensors, five NCCL collectives back to back; "
                          "'nccl' = views of one flat buffer, ONE NCCL collective; 'sym' = the flat buffer in symmetric memory, reduced by "
-                         "the library's multimem kernel.  Default: 'sym' from 8 ranks on, else 'off'")
+                         "the library's multimem kernel; 'arena' = the first backward of a step writes into slices of a symmetric buffer "
+                         "that autograd adopts as .grad (no memset, no extra add), ONE own collective.  Default: 'arena' from 4 ranks "
+                         "on, else 'off'")
     ap.add_argument("--no-fused-optimizer", action="store_true",
                     help="N>1, train leg: NCCL all-reduce + Adam on every rank instead of the fused multimem optimiser kernel")
     ap.add_argument("--no-balance", action="store_true",
