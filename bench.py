@@ -5,9 +5,12 @@
     python bench.py --impl reference --gpus N --steps K ...   # CPU arm: oracle/_cpu (C/OpenMP port) on host cores
 
 A "step" = every rank renders `views_per_rank` 1920x1080 views of the replicated 1 M-Gaussian SH-3 scene
-forward + backward (gradients w.r.t. all five activated tensors accumulate), and, for N>1, ONE NCCL
-all-reduce of the flat gradient buffer.  value = all ranks' pixels / max-over-ranks device time.
-Prints ONE JSON line on rank 0 (keys: see DESIGN.md "Measurement").
+forward + backward (gradients w.r.t. all five activated tensors accumulate), and, for N>1, the sum-all-reduce of
+the gradient (five NCCL collectives below 4 ranks; from 4 ranks on this library's own multimem kernel over a
+symmetric buffer the .grad tensors live in — GradientArena).  value = all ranks' pixels / max-over-ranks device time.
+Prints ONE JSON line on rank 0 (keys: see DESIGN.md "Measurement"): value / value_one_stream / e2e / roofline /
+cpu_baseline / reference_trainer (the reference's unmodified _training_step on this backend) / f1_store_path /
+train_step / multi_gpu diagnostics / oracle_pin.
 """
 from __future__ import annotations
 
