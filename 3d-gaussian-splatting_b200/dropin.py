@@ -17,6 +17,7 @@ Nothing here touches the arithmetic; there is no CPU fallback (``B200Backend`` r
 """
 from __future__ import annotations
 
+import contextlib
 import importlib
 import importlib.util
 import os
@@ -169,6 +170,77 @@ def register(reference: Optional[str] = None):
 
     gr.GaussianRasterizer._initialize_backend = _initialize_backend
     return gr
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Driving the reference's own trainer objects with this backend (used by bench.py's `reference_trainer` leg and by the
+# drop-in tests; no oracle, no CPU path involved)
+# ------------------------------------------------------------------------------------------------------------------
+REFERENCE_PARAM_KEYS = ("xyz", "features_dc", "features_rest", "opacity", "scaling", "rotation")
+
+
+def reference_available() -> bool:
+    try:
+        return reference_root() is not None
+    except RuntimeError:
+        return False
+
+
+def reference_modules():
+    """(rasterizer module, trainer module, model module, config module) of the UNMODIFIED reference, with B200Backend
+    registered at gaussian_rasterizer.py:97-118."""
+    gr = register()
+    tr = importlib.import_module("src.training.trainer")
+    gm = importlib.import_module("src.gaussians.gaussian_model")
+    cfg = importlib.import_module("src.gaussians.training_config")
+    return gr, tr, gm, cfg
+
+
+@contextlib.contextmanager
+def backend_override(gr, factory):
+    """Temporarily make GaussianRasterizer hand out ``factory(K)`` (None = leave the registered B200Backend)."""
+    if factory is None:
+        yield
+        return
+    saved = gr.GaussianRasterizer._initialize_backend
+    gr.GaussianRasterizer._initialize_backend = lambda self, backend, K: factory(K)
+    try:
+        yield
+    finally:
+        gr.GaussianRasterizer._initialize_backend = saved
+
+
+def make_reference_trainer(start, K, device: str, backend_factory=None, mixed_precision=None, **config_overrides):
+    """The reference's GaussianTrainer / GaussianModel / Adam (``_setup_optimizer``, trainer.py:331-340) /
+    GaussianRasterizer(..., backend="gsplat") (trainer.py:706-708), all unmodified, holding the raw parameters ``start``
+    (dict over REFERENCE_PARAM_KEYS).  ``backend_factory``: K -> backend object, for a comparator arm (tests)."""
+    import torch
+    gr, tr, gm, cfg = reference_modules()
+    config = cfg.TrainingConfig()
+    config.wandb_mode = "disabled"
+    if mixed_precision is not None:
+        config.use_mixed_precision = bool(mixed_precision)
+    for k, v in config_overrides.items():
+        if not hasattr(config, k):
+            raise AttributeError(f"TrainingConfig has no field {k}")
+        setattr(config, k, v)
+    trainer = tr.GaussianTrainer(config, device=device, wandb_run=None)
+    n = start["xyz"].shape[0]
+    model = gm.GaussianModel(n_gaussians=n, device=device)
+    with torch.no_grad():
+        for k in REFERENCE_PARAM_KEYS:
+            getattr(model, k).data = start[k].to(device=device, dtype=torch.float32).clone()
+    optimizer = trainer._setup_optimizer(model)
+    with backend_override(gr, backend_factory):
+        rasterizer = gr.GaussianRasterizer(K=K.to(device), device=device, enable_caching=True, backend="gsplat")
+    return trainer, model, optimizer, rasterizer
+
+
+def tensor_views(cams, images, K, W: int, H: int, device: str):
+    """What ``_to_tensor_view`` (trainer.py:270-281) builds per frame."""
+    import torch
+    return [{"image": img.to(device=device, dtype=torch.float32), "pose": vm.to(device=device, dtype=torch.float32),
+             "K": K.to(device=device, dtype=torch.float32), "width": W, "height": H} for vm, img in zip(cams, images)]
 
 
 def main(argv=None) -> int:

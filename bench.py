@@ -581,12 +581,11 @@ def run_b200(args):
     ref_trainer = None
     if world == 1 and not args.no_reference_trainer:
         try:
-            sys.path.insert(0, os.path.join(ROOT, "tests"))
-            import dropin_harness as dh
+            dh = pkg.dropin  # launcher utilities of the package (no oracle, no tests/ import on this arm)
             if not dh.reference_available():
                 raise LookupError("reference tree not staged (baseline/stage_reference.py runs in the build container)")
-            start = {k: sc[k] for k in dh.KEYS}
-            trainer, model, opt, rast = dh.make_trainer(start, sc["K"], "cuda", batch_size=V)
+            start = {k: sc[k] for k in dh.REFERENCE_PARAM_KEYS}
+            trainer, model, opt, rast = dh.make_reference_trainer(start, sc["K"], "cuda", batch_size=V)
             trainer.iteration = 10 ** 6  # SH schedule saturated: degree 3, as in every other leg
             assert isinstance(rast.backend, pkg.B200Backend)
             gts = [torch.rand(H, W, 3, generator=gen) for _ in range(2)]

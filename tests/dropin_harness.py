@@ -33,23 +33,12 @@ PKG = "3d-gaussian-splatting_b200"
 KEYS = ("xyz", "features_dc", "features_rest", "opacity", "scaling", "rotation")
 
 
-def reference_available() -> bool:
-    pkg = importlib.import_module(PKG)
-    try:
-        return pkg.dropin.reference_root() is not None
-    except RuntimeError:
-        return False
-
-
-def reference():
-    """(rasterizer module, trainer module, model module, config module) of the UNMODIFIED reference, with
-    B200Backend registered at gaussian_rasterizer.py:97-118."""
-    pkg = importlib.import_module(PKG)
-    gr = pkg.dropin.register()
-    tr = importlib.import_module("src.training.trainer")
-    gm = importlib.import_module("src.gaussians.gaussian_model")
-    cfg = importlib.import_module("src.gaussians.training_config")
-    return gr, tr, gm, cfg
+_pkg = importlib.import_module(PKG)
+reference_available = _pkg.dropin.reference_available
+reference = _pkg.dropin.reference_modules          # (rasterizer, trainer, model, config modules) with B200Backend registered
+backend_override = _pkg.dropin.backend_override
+make_trainer = _pkg.dropin.make_reference_trainer  # a real GaussianTrainer + GaussianModel + Adam + GaussianRasterizer
+tensor_views = _pkg.dropin.tensor_views
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -90,20 +79,6 @@ class OracleBackend:
                                   gaussian_params["opacities"], gaussian_params["shs"],
                                   viewpoint["world_view_transform"], self.K, W, H, int(sh_degree), bg)
         return {"render": img}
-
-
-@contextlib.contextmanager
-def backend_override(gr, factory: Optional[Callable]):
-    """Temporarily make GaussianRasterizer hand out ``factory(K)`` (None = leave the registered B200Backend)."""
-    if factory is None:
-        yield
-        return
-    saved = gr.GaussianRasterizer._initialize_backend
-    gr.GaussianRasterizer._initialize_backend = lambda self, backend, K: factory(K)
-    try:
-        yield
-    finally:
-        gr.GaussianRasterizer._initialize_backend = saved
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -181,39 +156,6 @@ def synthetic_capture(outdir: str, render_fn: Callable, truth: Dict[str, torch.T
         pickle.dump({"poses": poses, "intrinsics": K.double().numpy(), "frame_indices": list(range(len(cams))),
                      "video_path": video, "points_3d": pts, "colors": cols}, f)
     return dict(merged_data=merged, video=video, sfm_pkl=sfm_pkl, frames=frames, codec=codec, K=K, cams=cams)
-
-
-# ------------------------------------------------------------------------------------------------------------
-# a real trainer on a device
-# ------------------------------------------------------------------------------------------------------------
-def make_trainer(start: Dict[str, torch.Tensor], K: torch.Tensor, device: str, backend_factory: Optional[Callable] = None,
-                 mixed_precision: Optional[bool] = None, **config_overrides):
-    """The reference's GaussianTrainer / GaussianModel / Adam / GaussianRasterizer, all unmodified, holding ``start``."""
-    gr, tr, gm, cfg = reference()
-    config = cfg.TrainingConfig()
-    config.wandb_mode = "disabled"
-    if mixed_precision is not None:
-        config.use_mixed_precision = bool(mixed_precision)
-    for k, v in config_overrides.items():
-        if not hasattr(config, k):
-            raise AttributeError(f"TrainingConfig has no field {k}")
-        setattr(config, k, v)
-    trainer = tr.GaussianTrainer(config, device=device, wandb_run=None)
-    n = start["xyz"].shape[0]
-    model = gm.GaussianModel(n_gaussians=n, device=device)
-    with torch.no_grad():
-        for k in KEYS:
-            getattr(model, k).data = start[k].to(device=device, dtype=torch.float32).clone()
-    optimizer = trainer._setup_optimizer(model)
-    with backend_override(gr, backend_factory):
-        rasterizer = gr.GaussianRasterizer(K=K.to(device), device=device, enable_caching=True, backend="gsplat")
-    return trainer, model, optimizer, rasterizer
-
-
-def tensor_views(cams: torch.Tensor, images: List[torch.Tensor], K: torch.Tensor, W: int, H: int, device: str):
-    """What ``_to_tensor_view`` (trainer.py:270-281) builds per frame."""
-    return [{"image": img.to(device=device, dtype=torch.float32), "pose": vm.to(device=device, dtype=torch.float32),
-             "K": K.to(device=device, dtype=torch.float32), "width": W, "height": H} for vm, img in zip(cams, images)]
 
 
 # ------------------------------------------------------------------------------------------------------------
