@@ -337,7 +337,7 @@ def set_gradient_arena(arena) -> None:
     _GRAD_ARENA = arena
 
 
-_ACC_EVENTS = {}  # (device, gradient-buffer address) -> event after the last in-place accumulation into it
+_ACC_EVENTS = {}  # bare grad_into buffers only: (device, address) -> {"acc_event": event after the last in-place accumulation}
 
 
 class RasterizeSplats(torch.autograd.Function):
@@ -433,12 +433,14 @@ class RasterizeSplats(torch.autograd.Function):
                     v_scales = torch.empty_like(scales)
                     v_opac = torch.empty_like(opacities)
                     v_colors = torch.empty_like(colors)
-            acc_key = None
+            acc_holder = None
             if grad_into is not None:
                 # the in-place "+=" of the accumulate mode is not atomic: views in flight on different streams
-                # (streams.ViewStreams) take turns on the gradient buffer
-                acc_key = (dev.index, v_means.data_ptr())
-                prev = _ACC_EVENTS.get(acc_key)
+                # (streams.ViewStreams) take turns on the gradient buffer.  The event of the last accumulation lives WITH the
+                # buffer's owner (the store's grad-state dict: it dies with the buffer, so a re-allocated store can never meet
+                # a stale event); callers that pass bare buffers share one slot per (device, address)
+                acc_holder = state if state is not None else _ACC_EVENTS.setdefault((dev.index, v_means.data_ptr()), {})
+                prev = acc_holder.get("acc_event")
                 if prev is not None:
                     torch.cuda.current_stream().wait_event(prev)
             with _stage("project_sh_bwd"):
@@ -455,12 +457,10 @@ class RasterizeSplats(torch.autograd.Function):
                                                   _ptr(v_splats), _ptr(v_means), _ptr(v_quats), _ptr(v_scales), _ptr(v_opac),
                                                   _ptr(v_colors), st), "b200_project_sh_bwd")
         if grad_into is not None:
-            if len(_ACC_EVENTS) > 64:
-                _ACC_EVENTS.clear()
-            ev = _ACC_EVENTS.get(acc_key) or torch.cuda.Event()
+            ev = acc_holder.get("acc_event") or torch.cuda.Event()
             with torch.cuda.device(dev):
                 ev.record()
-            _ACC_EVENTS[acc_key] = ev
+            acc_holder["acc_event"] = ev
             return (None,) * 15
         return v_means, v_quats, v_scales, v_opac, v_colors, None, None, None, None, None, None, None, None, None, None
 
