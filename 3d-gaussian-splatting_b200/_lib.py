@@ -37,6 +37,7 @@ SIGNATURES = {
     "b200_tile_prep": (_i, [_p, _i, _i, _p, _p, _p, _p]),
     "b200_sort_pairs_k16_prepared": (_i, [_p, _p, _p, _p, _l, _i, _p, _p, _z, _p, _p]),
     "b200_sort_pairs_k32": (_i, [_p, _p, _p, _p, _l, _i, _p, _z, _p, _p]),
+    "b200_sort_pairs_k32_static": (_i, [_p, _p, _p, _p, _l, _i, _p, _p]),
     "b200_sort_pairs_k16": (_i, [_p, _p, _p, _p, _l, _i, _p, _z, _p, _p]),
     "b200_bin_count_sorted": (_i, [_p, _p, _l, _p, _p]),
     "b200_bin_emit_sorted": (_i, [_p, _p, _p, _p, _p, _l, _i, _i, _l, _p, _p, _p]),

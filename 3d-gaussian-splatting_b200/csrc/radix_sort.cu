@@ -416,3 +416,46 @@ extern "C" int b200_sort_pairs_k16_prepared(uint16_t* keys_a, uint32_t* vals_a, 
     return sort_pairs_impl<uint16_t>(keys_a, vals_a, keys_b, vals_b, M, end_bit, scratch, scratch_bytes, result_in_b_host, stream,
                                      "b200_sort_pairs_k16_prepared", digit_base);
 }
+
+// ---- allocation-free variant (no counterpart in the reference) ---------
+// b200_sort_pairs_k32 with its scratch (digit histograms, tile tickets, look-back status words) in a file-scope device
+// array instead of a caller buffer, for callers that cannot allocate (CUDA graph capture, serving loops).  Every GPU that
+// loads the library holds the array (2 105 600 B) until exit.  All calls share it: sort_pairs_impl clears the part a call
+// uses on `stream` before the first kernel, so stale contents of an earlier call never matter, but two calls that overlap
+// on the GPU (different streams, no ordering between them) race.
+#define RS_STATIC_TILES ((B200_SORT_STATIC_MAX_KEYS + RS_TILE - 1) / RS_TILE)
+#define RS_STATIC_BYTES ((((size_t)RS_MAX_PASSES * RS_RADIX * 4 + 256 + (size_t)RS_MAX_PASSES * RS_STATIC_TILES * RS_RADIX * 4) + 255) / 256 * 256)
+static __device__ __align__(256) unsigned char g_sort_static_scratch[RS_STATIC_BYTES];
+
+extern "C" int b200_sort_pairs_k32_static(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b, int64_t M,
+                                          int end_bit, int* result_in_b_host, void* stream) {
+    if (M > (int64_t)B200_SORT_STATIC_MAX_KEYS) {
+        b200_set_error("b200_sort_pairs_k32_static: M = %lld exceeds the static scratch (B200_SORT_STATIC_MAX_KEYS = %d keys)",
+                       (long long)M, (int)B200_SORT_STATIC_MAX_KEYS);
+        return B200_EARG;
+    }
+    // In host code the array's name is only a handle: the device address is asked for once per device, with that
+    // device current, and cached.
+    static void* dev_ptr[B200_MAX_DEVICES] = {};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= B200_MAX_DEVICES) {
+        b200_set_error("b200_sort_pairs_k32_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+        return B200_ECUDA;
+    }
+    if (dev_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_sort_static_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            b200_set_error("b200_sort_pairs_k32_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            return B200_ECUDA;
+        }
+        dev_ptr[dev] = p;
+    }
+    if (b200_sort_scratch_bytes(B200_SORT_STATIC_MAX_KEYS) > RS_STATIC_BYTES) {  // layout drifted from the array's size
+        b200_set_error("b200_sort_pairs_k32_static: static scratch smaller than b200_sort_scratch_bytes(max)");
+        return B200_ESCRATCH;
+    }
+    return sort_pairs_impl<uint32_t>(keys_a, vals_a, keys_b, vals_b, M, end_bit, dev_ptr[dev], RS_STATIC_BYTES,
+                                     result_in_b_host, stream, "b200_sort_pairs_k32_static");
+}

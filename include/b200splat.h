@@ -125,6 +125,17 @@ int b200_sort_pairs_k16(uint16_t* keys_a, uint32_t* vals_a, uint16_t* keys_b, ui
                         int64_t M, int end_bit, void* scratch, size_t scratch_bytes,
                         int* result_in_b_host, void* stream);
 
+/* Allocation-free variant of b200_sort_pairs_k32.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, serving loops, harnesses
+ * that forbid it).  Same contract and same result as b200_sort_pairs_k32, but the scratch lives in a
+ * file-scope device array inside the library (2 105 600 B, held by every GPU that loads the library until
+ * exit); nothing is allocated or freed by the call.  M > B200_SORT_STATIC_MAX_KEYS is rejected (B200_EARG).
+ * Every call shares the array; each call clears what it uses on `stream` first, so calls ordered on the
+ * GPU are independent, but calls that OVERLAP on the GPU (different streams without ordering) race. */
+#define B200_SORT_STATIC_MAX_KEYS 1048576
+int b200_sort_pairs_k32_static(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b,
+                               int64_t M, int end_bit, int* result_in_b_host, void* stream);
+
 /* ---- stage 2b'/2c': split-key form of the same sort (the fast path) ----------------------------
  * An LSD radix sort of (tile<<32 | depth) keys visits the depth digits first and the tile digits
  * last.  Depth digits do not depend on the tile, so they are sorted over the N Gaussians BEFORE the
