@@ -37,7 +37,7 @@ def rows_ok(got, ref, rtol=1e-3, floor=1e-2):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=1_000_000)
+    ap.add_argument("--gaussians", dest="n", type=int, default=1_000_000)  # not "--n": torchrun's own parser would claim it as an abbreviation
     ap.add_argument("--views-per-rank", type=int, default=2)
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)

@@ -25,7 +25,7 @@ def _torchrun(script, *args, port=29541):
 
 @needs_two
 def test_reduced_gradient_equals_single_rank_gradient_and_replicas_stay_identical():
-    rc, out = _torchrun("multi_gpu_check.py", "--n", "200000", "--width", "960", "--height", "540", port=29541)
+    rc, out = _torchrun("multi_gpu_check.py", "--gaussians", "200000", "--width", "960", "--height", "540", port=29541)
     print(out["all_ranks"])
     assert rc == 0 and out["ok"] and out["all_ranks"]["bit_identical"] and out["all_ranks"]["min_rows_ok"] >= 0.999
 

@@ -144,6 +144,11 @@ def test_second_device_in_the_same_process(pkg, oracle):
         res = be.render_with_depth(leaves, vp, bg_color=torch.zeros(3, device=d), render_mode="RGB", device=d, sh_degree=3)
         res["render"].sum().backward()
         torch.cuda.synchronize(d)
-        outs.append((res["render"].detach().cpu(), leaves["means3D"].grad.cpu()))
+        outs.append((res["render"].detach().cpu(), {k: v.grad.cpu() for k, v in leaves.items()}))
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][0], outs[2][0])
-    assert torch.allclose(outs[0][1], outs[1][1], rtol=1e-4, atol=1e-6)
+    # gradients are sums of atomics: two runs differ by the summation order, on one device as much as across devices
+    # (profiles/two_device_probe.py on 2 x B200: <= 3.1e-7 of the tensor's largest entry either way) -> bar 1e-5 of it
+    for a, b in ((0, 1), (0, 2)):
+        for k in outs[0][1]:
+            ref = outs[a][1][k]
+            assert (ref - outs[b][1][k]).abs().max().item() <= 1e-5 * ref.abs().max().item(), (a, b, k)
