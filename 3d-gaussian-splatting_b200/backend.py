@@ -9,7 +9,7 @@ from typing import Dict
 
 import torch
 
-from .rasterization import rasterization
+from .rasterization import _render_one, rasterization
 
 
 class B200Backend:
@@ -87,14 +87,24 @@ class B200Backend:
         if sh_degree is None:
             sh_degree = 3 if "shs" in gaussian_params else None
         viewmat = viewpoint["world_view_transform"]
-        renders, alphas, meta = self.rasterization(
-            means=means3D, quats=quats, scales=scales, opacities=opacities, colors=colors,
-            viewmats=viewmat[None, ...], Ks=self.K[None, ...],
-            width=viewpoint["image_width"], height=viewpoint["image_height"], packed=False,
-            render_mode=render_mode, sh_degree=sh_degree, backgrounds=bg_color[None, ...],
-        )
-        output = renders.squeeze(0)  # one camera: squeeze is a view both ways (select's backward = zeros + full-image copy)
-        alpha = alphas.squeeze(0)
+        if render_mode not in ("RGB", "D", "ED", "RGB+D", "RGB+ED"):
+            raise ValueError(f"render_mode must be one of RGB, D, ED, RGB+D, RGB+ED, got {render_mode!r}")
+        if self.rasterization is rasterization and viewmat.dim() == 2 and bg_color.dim() == 1:
+            # the same call without the round trip through the gsplat-shaped signature ([None] on the way in, squeeze(0) /
+            # [0] on the way out: a dozen tensor views per view on the host and two extra nodes in the backward graph)
+            output, alpha, aux = _render_one(means3D, quats, scales, opacities, colors, viewmat, self.K,
+                                             viewpoint["image_width"], viewpoint["image_height"], sh_degree, render_mode,
+                                             bg_color, 0.01, 1e10, 0.3, 0.0)
+            meta = None
+        else:
+            renders, alphas, meta = self.rasterization(
+                means=means3D, quats=quats, scales=scales, opacities=opacities, colors=colors,
+                viewmats=viewmat[None, ...], Ks=self.K[None, ...],
+                width=viewpoint["image_width"], height=viewpoint["image_height"], packed=False,
+                render_mode=render_mode, sh_degree=sh_degree, backgrounds=bg_color[None, ...],
+            )
+            output = renders.squeeze(0)  # one camera: squeeze is a view both ways (select's backward = zeros + full-image copy)
+            alpha = alphas.squeeze(0)
         result = {"alpha": alpha}
         if render_mode == "RGB":
             result["render"] = output
@@ -108,6 +118,11 @@ class B200Backend:
         elif render_mode == "RGB+ED":
             result["render"] = output[..., :3]
             result["expected_depth"] = output[..., 3]
+        if meta is None:
+            result["means2d"] = aux["splats"][:, 0:2]
+            result["radii"] = aux["radii"]
+            result["visibility_filter"] = aux["visibility"]  # = radii > 0, from the projection kernel
+            return result
         if "means2d" in meta:
             result["means2d"] = meta["means2d"][0]
         if "radii" in meta:

@@ -11,6 +11,7 @@ hand-written sm_100a kernel reached through ``libb200splat.so``.  No CPU path ex
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 import math
 import os
@@ -51,6 +52,14 @@ def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 
 
+_NO_GUARD = contextlib.nullcontext()
+
+
+def _on_device(dev: torch.device):
+    """``torch.cuda.device(dev)`` that costs nothing when ``dev`` is already current (the usual case)."""
+    return _NO_GUARD if torch.cuda.current_device() == dev.index else torch.cuda.device(dev)
+
+
 def _require_cuda(*tensors: torch.Tensor) -> torch.device:
     dev = tensors[0].device
     for t in tensors:
@@ -64,6 +73,11 @@ def _require_cuda(*tensors: torch.Tensor) -> torch.device:
     return dev
 
 
+def _plain_f32(t: torch.Tensor, dev: torch.device) -> bool:
+    """Usable by address as it is (the common case: skips three no-op torch calls per tensor on the host path)."""
+    return t.dtype == torch.float32 and t.device == dev and t.is_contiguous()
+
+
 def make_cam(viewmat: torch.Tensor, K: torch.Tensor, width: int, height: int, near_plane: float = 0.01,
              far_plane: float = 1e10, eps2d: float = 0.3, radius_clip: float = 0.0) -> torch.Tensor:
     """Packed DEVICE camera block (include/b200splat.h, b200_cam_pack).  The pose and the intrinsics are
@@ -74,14 +88,18 @@ def make_cam(viewmat: torch.Tensor, K: torch.Tensor, width: int, height: int, ne
         dev = viewmat.device
     elif K.device.type == "cuda":
         dev = K.device
-    vm = viewmat.detach().to(device=dev, dtype=torch.float32).contiguous()
-    Kd = K.detach().to(device=dev, dtype=torch.float32).contiguous()
+    vm = viewmat if _plain_f32(viewmat, dev) else viewmat.detach().to(device=dev, dtype=torch.float32).contiguous()
+    Kd = K if _plain_f32(K, dev) else K.detach().to(device=dev, dtype=torch.float32).contiguous()
     if vm.numel() != 16 or Kd.numel() != 9:
         raise ValueError("make_cam: viewmat must be [4,4] and K [3,3]")
     cam = torch.empty(_lib.CAM_DEV_FLOATS, dtype=torch.float32, device=dev)
-    with torch.cuda.device(dev):
+    if torch.cuda.current_device() == dev.index:
         check(lib.b200_cam_pack(_ptr(vm), _ptr(Kd), float(near_plane), float(far_plane), float(eps2d),
                                 float(radius_clip), int(width), int(height), _ptr(cam), _stream()), "b200_cam_pack")
+    else:
+        with torch.cuda.device(dev):
+            check(lib.b200_cam_pack(_ptr(vm), _ptr(Kd), float(near_plane), float(far_plane), float(eps2d),
+                                    float(radius_clip), int(width), int(height), _ptr(cam), _stream()), "b200_cam_pack")
     return cam
 
 
@@ -128,6 +146,146 @@ def _sort_scratch(M: int, dev) -> torch.Tensor:
     return torch.empty(max(int(lib.b200_sort_scratch_bytes(M)), 256), dtype=torch.uint8, device=dev)
 
 
+_COARSE_OK = {}
+
+
+def _coarse_supported(width: int, height: int) -> bool:
+    """Two-level binning available for this image size (tile grid within b200_tile_prep / b200_bin_coarse limits)."""
+    ok = _COARSE_OK.get((width, height))
+    if ok is None:
+        tile_w, tile_h = (width + _lib.TILE - 1) // _lib.TILE, (height + _lib.TILE - 1) // _lib.TILE
+        ok = bool(lib.b200_bin_coarse_supported(width, height)) and \
+            (tile_w + 1) * (tile_h + 1) <= int(lib.b200_tile_prep_max_cells()) and tile_w * tile_h <= 65536
+        _COARSE_OK[(width, height)] = ok
+    return ok
+
+
+def _carve(dev: torch.device, sizes):
+    """ONE allocation for buffers that die with the call: returns (owner tensor, device addresses), 256-B aligned."""
+    offs, total = [], 0
+    for b in sizes:
+        offs.append(total)
+        total += (max(int(b), 0) + 255) & ~255
+    owner = torch.empty(max(total, 256), dtype=torch.uint8, device=dev)
+    base = owner.data_ptr()
+    return owner, [base + o for o in offs]
+
+
+# B200_FRONT_PRIORITY=1: the kernels up to the read-back of M (projection, tile_count, tile_prep) and the sorts / binning run
+# on HIGH-PRIORITY companions of the caller's stream.  With the views of a step in flight on alternating streams
+# (streams.ViewStreams) the block scheduler then places their few CTAs as soon as CTAs of the other view's blend retire
+# instead of behind that blend's last CTA, which is what the host waits for before it can size the intersection buffers.
+# Memory stays in the caller's stream pool (only the launches move), ordered by events both ways.
+FRONT_PRIORITY = int(os.environ.get("B200_FRONT_PRIORITY", "0"))
+_FRONT_STREAMS = {}
+
+
+def _front_stream(dev: torch.device, cur: torch.cuda.Stream) -> torch.cuda.Stream:
+    key = (dev.index, cur.cuda_stream)
+    s = _FRONT_STREAMS.get(key)
+    if s is None:
+        s = torch.cuda.Stream(device=dev, priority=-1)
+        _FRONT_STREAMS[key] = s
+    return s
+
+
+def _project_and_bin_coarse(means, quats, scales, opacities, colors, sh_coeffs: int, deg: int, cam, width: int, height: int,
+                            tile_w: int, tile_h: int, N: int, raw: bool, want_grad_records: bool, coarse_gather: bool,
+                            with_isect_ids: bool, dev: torch.device) -> Dict[str, torch.Tensor]:
+    """The default path of project_and_bin (method "coarse"), written for a short HOST path: the tensors that outlive the call
+    are allocated one by one, everything else lives in two carved workspaces addressed by raw pointers; the side-stream
+    kernels are launched by stream handle (no stream context switch); M arrives in pinned host memory written by
+    b200_tile_prep itself (unified addressing: the pinned scalar is device-visible), so there is no copy to enqueue."""
+    n_tiles = tile_w * tile_h
+    cur = torch.cuda.current_stream(dev)
+    launch = cur
+    if FRONT_PRIORITY:
+        launch = _front_stream(dev, cur)
+        enter = torch.cuda.Event()
+        enter.record(cur)
+        launch.wait_event(enter)
+    st = launch.cuda_stream
+    n1 = max(N, 1)
+    i32, f32 = torch.int32, torch.float32
+    radii = torch.empty(N, 2, dtype=i32, device=dev)
+    splats = torch.empty(N, _lib.SPLAT_FLOATS, dtype=f32, device=dev)
+    tiles_per_gauss = torch.empty(N, dtype=i32, device=dev)
+    visibility = torch.empty(N, 2, dtype=torch.bool, device=dev)
+    grad_records = torch.empty(N, _lib.SPLAT_FLOATS, dtype=f32, device=dev) if want_grad_records else None
+    offsets = torch.empty(n_tiles, dtype=i32, device=dev)
+    sort_bytes = max(int(lib.b200_sort_scratch_bytes(N)), 256)
+    ws1, (p_dkeys_a, p_gids_a, p_dkeys_b, p_gids_b, p_rects, p_grid, p_digit, p_sort) = _carve(
+        dev, (4 * n1, 4 * n1, 4 * n1, 4 * n1, 0 if coarse_gather else 8 * n1, 4 * (tile_h + 1) * (tile_w + 1), 4 * 512, sort_bytes))
+    if coarse_gather:
+        p_rects = None
+    project_fwd = lib.b200_project_sh_fwd_raw if raw else lib.b200_project_sh_fwd  # raw: activations fused in
+    with _stage("project_sh_fwd"):
+        check(project_fwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors), sh_coeffs, deg, N, None,
+                          _ptr(cam), width, height, _ptr(radii), _ptr(splats), _ptr(tiles_per_gauss), None, p_dkeys_a, p_gids_a,
+                          None if GRID_ON_SIDE_STREAM else p_grid, _ptr(visibility), _ptr(grad_records), p_rects, st),
+              "b200_project_sh_fwd", kernels=1 if N > 0 else 0)
+    # tile_count + tile_prep (one CTA: 2-D prefix sum of the corner grid -> per-tile ranges, digit bases, M) depend only on the
+    # projection: they go on a side stream and run under the depth sort.  The launching stream joins before it first needs
+    # the ranges; the host collects M after the depth-sort launches are queued, so it never waits on an idle GPU.
+    side = _side_stream(dev)
+    fork = torch.cuda.Event()
+    fork.record(launch)
+    side.wait_event(fork)
+    sst = side.cuda_stream
+    m_host = _pinned_scalar(dev)
+    timed = _lib.stage_timer is not None  # bench's per-stage events are recorded on the CURRENT stream
+    if timed:
+        torch.cuda.set_stream(side)
+    try:
+        if GRID_ON_SIDE_STREAM:  # the corner grid is counted here, not inside the projection kernel (b200_tile_count)
+            with _stage("tile_count"):
+                check(lib.b200_tile_count(_ptr(splats), _ptr(radii), N, width, height, p_grid, sst), "b200_tile_count",
+                      kernels=1 if N > 0 else 0)
+        with _stage("tile_prep"):
+            check(lib.b200_tile_prep(p_grid, width, height, _ptr(offsets), m_host.data_ptr(), p_digit, sst), "b200_tile_prep")
+    finally:
+        if timed:
+            torch.cuda.set_stream(cur)
+    m_ready = torch.cuda.Event()
+    m_ready.record(side)
+    in_b = C.c_int(0)
+    if timed and launch is not cur:
+        torch.cuda.set_stream(launch)
+    try:
+        with _stage("sort_depth"):
+            check(lib.b200_sort_pairs_k32(p_dkeys_a, p_gids_a, p_dkeys_b, p_gids_b, N, 32, p_sort, sort_bytes, C.byref(in_b), st),
+                  "b200_sort_pairs_k32", kernels=6 if N > 0 else 0)
+        p_perm = p_gids_b if in_b.value else p_gids_a
+        launch.wait_event(m_ready)  # join: ranges / digit bases are used from here on
+        m_ready.synchronize()  # the one host wait of the forward pass (sizes the intersection buffers)
+        M = int(m_host.item())
+        cap = max(M, 1)
+        flat_ids = torch.empty(cap, dtype=i32, device=dev)
+        sb = max(int(lib.b200_bin_coarse_scratch_bytes(N, M)), 256)
+        ws2, (p_k0, p_k1, p_k2, p_k3, p_scr) = _carve(dev, (4 * cap, 4 * cap, 4 * cap, 4 * cap, sb))
+        with _stage("bin_coarse"):
+            check(lib.b200_bin_coarse(_ptr(splats), _ptr(radii), p_rects, p_perm, N, width, height, _ptr(offsets), M,
+                                      p_k0, p_k1, p_k2, p_k3, _ptr(flat_ids), p_scr, sb, st), "b200_bin_coarse",
+                  kernels=(3 + (2 if n_tiles > 16 * 256 else 1)) if (N > 0 and M > 0) else 0)
+        ids = None
+        if with_isect_ids:
+            ids = torch.empty(cap, dtype=torch.int64, device=dev)
+            check(lib.b200_isect_ids_from_offsets(_ptr(flat_ids), _ptr(offsets), n_tiles, _ptr(splats), M, _ptr(ids), st),
+                  "b200_isect_ids_from_offsets", kernels=1 if M > 0 else 0)
+            ids = ids[:M]
+    finally:
+        if timed and launch is not cur:
+            torch.cuda.set_stream(cur)
+    if launch is not cur:
+        leave = torch.cuda.Event()
+        leave.record(launch)
+        cur.wait_event(leave)
+    del ws1, ws2  # freed in the caller's stream order, after the join above
+    return dict(radii=radii, splats=splats, tiles_per_gauss=tiles_per_gauss, tile_w=tile_w, tile_h=tile_h,
+                visibility=visibility, grad_records=grad_records, M=M, flatten_ids=flat_ids[:M],
+                isect_offsets=offsets.view(tile_h, tile_w), tile_keys=None, isect_ids=ids)
+
+
 def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional[int], cam, width: int,
                     height: int, keep_unsorted: bool = False, method: str = "auto",
                     with_isect_ids: bool = False, raw: bool = False, want_grad_records: bool = False) -> Dict[str, torch.Tensor]:
@@ -149,22 +307,23 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
     tile_w = (width + _lib.TILE - 1) // _lib.TILE
     tile_h = (height + _lib.TILE - 1) // _lib.TILE
     n_tiles = tile_w * tile_h
+    coarse_ok = _coarse_supported(int(width), int(height))
     if method == "auto":
         method = "split" if (n_tiles <= 65536 and not keep_unsorted) else "keys64"
-        if method == "split" and (tile_w + 1) * (tile_h + 1) <= int(lib.b200_tile_prep_max_cells()) \
-                and lib.b200_bin_coarse_supported(width, height):
+        if method == "split" and coarse_ok:
             method = "coarse"
     coarse_gather = method == "coarse-gather"  # "coarse" recomputing the rectangles from radii / means2d (test path)
     coarse = method in ("coarse", "coarse-gather")
-    if coarse:
-        if not lib.b200_bin_coarse_supported(width, height) or (tile_w + 1) * (tile_h + 1) > int(lib.b200_tile_prep_max_cells()):
-            raise ValueError("binning='coarse' needs a tile grid within b200_bin_coarse_supported / b200_tile_prep limits")
-        method = "split"  # same front half: depth keys, corner grid, tile_prep, depth sort
-    st = _stream()
     if sh_degree is None:
         sh_coeffs, deg = 1, -1
     else:
         sh_coeffs, deg = colors.shape[1], int(sh_degree)
+    if coarse:
+        if not coarse_ok:
+            raise ValueError("binning='coarse' needs a tile grid within b200_bin_coarse_supported / b200_tile_prep limits")
+        return _project_and_bin_coarse(means, quats, scales, opacities, colors, sh_coeffs, deg, cam, int(width), int(height),
+                                       tile_w, tile_h, N, raw, want_grad_records, coarse_gather, with_isect_ids, dev)
+    st = _stream()
     radii = torch.empty(N, 2, dtype=torch.int32, device=dev)
     splats = torch.empty(N, _lib.SPLAT_FLOATS, dtype=torch.float32, device=dev)
     tiles_per_gauss = torch.empty(N, dtype=torch.int32, device=dev)
@@ -184,7 +343,7 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
     # the zero-initialised cotangent records it accumulates into — two eager torch launches per view otherwise
     visibility = torch.empty(N, 2, dtype=torch.bool, device=dev)
     grad_records = torch.empty(N, _lib.SPLAT_FLOATS, dtype=torch.float32, device=dev) if want_grad_records else None
-    rects = torch.empty(N, 2, dtype=torch.int32, device=dev) if (coarse and not coarse_gather) else None  # packed tile rectangles
+    rects = None  # packed tile rectangles: the two-level path only (_project_and_bin_coarse)
     with _stage("project_sh_fwd"):
         check(project_fwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors),
                                       sh_coeffs, deg, N, None, _ptr(cam), width, height, _ptr(radii), _ptr(splats),
@@ -259,28 +418,6 @@ def project_and_bin(means, quats, scales, opacities, colors, sh_degree: Optional
     perm = gids_b if in_b.value else gids_a
     if prep:
         torch.cuda.current_stream(dev).wait_event(m_ready)  # join: ranges / digit bases are used from here on
-    if coarse:
-        m_ready.synchronize()  # the one host wait of the forward pass (sizes the intersection buffers)
-        M = int(m_host.item())
-        cap = max(M, 1)
-        ck = torch.empty(4, cap, dtype=torch.int32, device=dev)  # pair keys / ids, double-buffered (M' <= M used)
-        flat_ids = torch.empty(cap, dtype=torch.int32, device=dev)
-        sb = int(lib.b200_bin_coarse_scratch_bytes(N, M))
-        scratch_c = torch.empty(max(sb, 256), dtype=torch.uint8, device=dev)
-        with _stage("bin_coarse"):
-            check(lib.b200_bin_coarse(_ptr(splats), _ptr(radii), _ptr(rects), _ptr(perm), N, width, height,
-                                      _ptr(offsets), M, _ptr(ck[0]), _ptr(ck[1]), _ptr(ck[2]), _ptr(ck[3]), _ptr(flat_ids),
-                                      _ptr(scratch_c), scratch_c.numel(), st), "b200_bin_coarse",
-                  kernels=(3 + (2 if n_tiles > 16 * 256 else 1)) if (N > 0 and M > 0) else 0)
-        out.update(M=M, flatten_ids=flat_ids[:M], isect_offsets=offsets.view(tile_h, tile_w), tile_keys=None)
-        if with_isect_ids:
-            ids = torch.empty(cap, dtype=torch.int64, device=dev)
-            check(lib.b200_isect_ids_from_offsets(_ptr(flat_ids), _ptr(offsets), n_tiles, _ptr(splats), M, _ptr(ids), st),
-                  "b200_isect_ids_from_offsets", kernels=1 if M > 0 else 0)
-            out["isect_ids"] = ids[:M]
-        else:
-            out["isect_ids"] = None
-        return out
     with _stage("bin_scan"):
         check(lib.b200_bin_count_sorted(_ptr(tiles_per_gauss), _ptr(perm), N, _ptr(block_sums), st),
               "b200_bin_count_sorted", kernels=1 if N > 0 else 0)
@@ -340,14 +477,27 @@ def set_gradient_arena(arena) -> None:
 _ACC_EVENTS = {}  # bare grad_into buffers only: (device, address) -> {"acc_event": event after the last in-place accumulation}
 
 
+class _Aux:
+    """Holder for the non-differentiable by-products of one RasterizeSplats.forward (filled in place).  A plain object on
+    purpose: under autocast, custom_fwd's argument cast rebuilds dicts / lists, so a dict would be filled as a copy."""
+
+    __slots__ = ("radii", "splats", "tiles_per_gauss", "isect_ids", "flatten_ids", "isect_offsets", "last_ids", "visibility")
+
+    def __getitem__(self, key):
+        return getattr(self, key)
+
+
 class RasterizeSplats(torch.autograd.Function):
     """forward = stages 1-3, backward = stages 4a-4b (gsplat's autograd of rasterization())."""
 
     @staticmethod
     @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
     def forward(ctx, means, quats, scales, opacities, colors, cam, width, height, sh_degree, chset, background,
-                with_isect_ids=False, method="auto", raw=False, grad_into=None):
-        """raw=True: the five tensors are the RAW parameters (xyz, rotation, log-scaling, opacity logits,
+                with_isect_ids=False, method="auto", raw=False, grad_into=None, aux=None):
+        """Returns (render[H,W,CH], alpha[H,W,1]); the non-differentiable by-products (radii, splats, tiles_per_gauss,
+        isect_ids, flatten_ids, isect_offsets, last_ids, visibility) are put into the holder ``aux`` (:class:`_Aux`) instead of being
+        wrapped as autograd outputs (eight fewer output tensors to register per view on the host).
+        raw=True: the five tensors are the RAW parameters (xyz, rotation, log-scaling, opacity logits,
         features) and the activations are fused into the kernels.  grad_into = (g_xyz, g_rotation, g_scaling,
         g_opacity, g_features): backward ADDS the raw-parameter gradients into these buffers in place (and
         returns None for the inputs) instead of handing fresh tensors to autograd."""
@@ -358,7 +508,7 @@ class RasterizeSplats(torch.autograd.Function):
         if grad_into is not None and not raw:
             raise ValueError("grad_into needs raw=True")
         needs_grad = any(ctx.needs_input_grad[:5]) or grad_into is not None
-        with torch.cuda.device(dev):
+        with _on_device(dev):
             b = project_and_bin(means, quats, scales, opacities, colors, sh_degree, cam, width, height,
                                 method=method, with_isect_ids=with_isect_ids, raw=raw, want_grad_records=needs_grad)
             if b["isect_ids"] is None:
@@ -379,14 +529,14 @@ class RasterizeSplats(torch.autograd.Function):
         # (a second one, retain_graph=True, allocates its own)
         ctx.grad_records = b["grad_records"]
         ctx.set_materialize_grads(False)  # unused outputs hand backward() None instead of freshly zero-filled tensors
-        ctx.mark_non_differentiable(b["radii"], b["splats"], b["tiles_per_gauss"], b["isect_ids"],
-                                    b["flatten_ids"], b["isect_offsets"], last_ids, b["visibility"])
-        return (render, alpha, b["radii"], b["splats"], b["tiles_per_gauss"], b["isect_ids"], b["flatten_ids"],
-                b["isect_offsets"], last_ids, b["visibility"])
+        if aux is not None:
+            aux.radii, aux.splats, aux.tiles_per_gauss, aux.isect_ids = b["radii"], b["splats"], b["tiles_per_gauss"], b["isect_ids"]
+            aux.flatten_ids, aux.isect_offsets, aux.last_ids, aux.visibility = b["flatten_ids"], b["isect_offsets"], last_ids, b["visibility"]
+        return render, alpha
 
     @staticmethod
     @torch.amp.custom_bwd(device_type="cuda")
-    def backward(ctx, v_render, v_alpha, *_unused):
+    def backward(ctx, v_render, v_alpha):
         means, quats, scales, opacities, colors, radii, splats, flatten_ids, offsets, alpha, last_ids = ctx.saved_tensors
         cam, width, height, sh_degree, chset, bg, n_bg, M, raw, grad_into = ctx.cfg
         dev = means.device
@@ -397,7 +547,7 @@ class RasterizeSplats(torch.autograd.Function):
         v_render = v_render.to(torch.float32).contiguous()
         if v_alpha is not None:
             v_alpha = v_alpha.to(torch.float32).contiguous()
-        with torch.cuda.device(dev):
+        with _on_device(dev):
             st = _stream()
             v_splats, ctx.grad_records = ctx.grad_records, None
             if v_splats is None:
@@ -458,11 +608,11 @@ class RasterizeSplats(torch.autograd.Function):
                                                   _ptr(v_colors), st), "b200_project_sh_bwd")
         if grad_into is not None:
             ev = acc_holder.get("acc_event") or torch.cuda.Event()
-            with torch.cuda.device(dev):
+            with _on_device(dev):
                 ev.record()
             acc_holder["acc_event"] = ev
-            return (None,) * 15
-        return v_means, v_quats, v_scales, v_opac, v_colors, None, None, None, None, None, None, None, None, None, None
+            return (None,) * 16
+        return v_means, v_quats, v_scales, v_opac, v_colors, None, None, None, None, None, None, None, None, None, None, None
 
 
 def _render_one(means, quats, scales, opacities, colors, viewmat, K, width, height, sh_degree, render_mode,
@@ -474,18 +624,18 @@ def _render_one(means, quats, scales, opacities, colors, viewmat, K, width, heig
     if background is None or chset == _lib.CH_D:
         bg = (None, 0)
     else:
-        bgt = background.detach().reshape(-1).to(device=means.device, dtype=torch.float32).contiguous()
+        bgt = background if (background.dim() == 1 and _plain_f32(background, means.device)) else \
+            background.detach().reshape(-1).to(device=means.device, dtype=torch.float32).contiguous()
         if bgt.numel() < 3:
             raise ValueError("backgrounds must hold 3 colour channels")
         bg = (bgt, 3)
     cam = make_cam(viewmat, K, int(width), int(height), near_plane, far_plane, eps2d, radius_clip)
-    out = RasterizeSplats.apply(means, quats, scales, opacities, colors, cam, int(width), int(height), sh_degree,
-                                chset, bg, with_isect_ids, method, raw, grad_into)
-    render, alpha, radii, splats, tiles_per_gauss, isect_ids, flatten_ids, offsets, last_ids, visibility = out
+    aux = _Aux()
+    render, alpha = RasterizeSplats.apply(means, quats, scales, opacities, colors, cam, int(width), int(height), sh_degree,
+                                          chset, bg, with_isect_ids, method, raw, grad_into, aux)
     if render_mode in ("ED", "RGB+ED"):
         render = torch.cat([render[..., :-1], render[..., -1:] / alpha.clamp(min=1e-10)], dim=-1)
-    return render, alpha, dict(radii=radii, splats=splats, tiles_per_gauss=tiles_per_gauss, isect_ids=isect_ids,
-                               flatten_ids=flatten_ids, isect_offsets=offsets, last_ids=last_ids, visibility=visibility)
+    return render, alpha, aux
 
 
 def rasterization(means: torch.Tensor, quats: torch.Tensor, scales: torch.Tensor, opacities: torch.Tensor,

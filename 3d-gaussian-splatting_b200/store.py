@@ -26,7 +26,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-from .rasterization import rasterization
+from .rasterization import _render_one, rasterization
 
 _BLOCKS = (("xyz", 3), ("scaling", 3), ("rotation", 4), ("opacity", 1), ("features", 48))
 FLOATS_PER_GAUSSIAN = sum(w for _, w in _BLOCKS)  # 59
@@ -34,6 +34,24 @@ FLOATS_PER_GAUSSIAN = sum(w for _, w in _BLOCKS)  # 59
 
 def _align4(n: int) -> int:
     return (n + 3) // 4 * 4  # floats -> 16-byte multiples
+
+
+class GradState:
+    """Per-gradient-buffer state shared with the backward pass (lazy zero flag, event of the last in-place accumulation).
+    Deliberately NOT a Mapping / Iterable: under autocast, custom_fwd's argument cast rebuilds dicts, and the backward
+    would then flip ``pending_zero`` on a copy."""
+
+    def __init__(self, **kw):
+        self._d = dict(kw)
+
+    def get(self, key, default=None):
+        return self._d.get(key, default)
+
+    def __getitem__(self, key):
+        return self._d[key]
+
+    def __setitem__(self, key, value):
+        self._d[key] = value
 
 
 class GaussianStore(nn.Module):
@@ -80,7 +98,7 @@ class GaussianStore(nn.Module):
             self.flat, self._flat_grad = self._sym_flat.tensor, self._sym_grad.tensor
         # shared with the backward pass (rasterization.RasterizeSplats): True after zero_grad(lazy=True) until the first
         # backward has WRITTEN the buffer instead of adding into it
-        self._grad_state = {"pending_zero": False}
+        self._grad_state = GradState(pending_zero=False)
 
         def view(buf, name, *shape):
             w = dict(_BLOCKS)[name]
@@ -246,15 +264,26 @@ class GaussianStore(nn.Module):
         accumulate_grads=True: ``loss.backward()`` adds the parameter gradients into ``flat_grad`` (i.e. into every
         ``param.grad``) inside the backward kernel.  False: gradients flow through autograd as usual."""
         W, H = int(viewpoint["image_width"]), int(viewpoint["image_height"])
-        renders, alphas, meta = rasterization(
-            means=self.xyz, quats=self.rotation, scales=self.scaling, opacities=self.opacity.view(-1),
-            colors=self.features, viewmats=viewpoint["world_view_transform"][None], Ks=K[None], width=W, height=H,
-            sh_degree=sh_degree, render_mode=render_mode,
-            backgrounds=None if bg_color is None else bg_color[None], raw_params=True,
-            grad_into=self.grad_buffers() if (accumulate_grads and torch.is_grad_enabled()) else None)
-        out, alpha = renders.squeeze(0), alphas.squeeze(0)  # views both ways (select's backward = zeros + full-image copy)
-        result = {"alpha": alpha, "means2d": meta["means2d"][0], "radii": meta["radii"][0]}
-        result["visibility_filter"] = meta["visibility_filter"][0]  # = radii > 0, from the projection kernel
+        viewmat = viewpoint["world_view_transform"]
+        grad_into = self.grad_buffers() if (accumulate_grads and torch.is_grad_enabled()) else None
+        if render_mode not in ("RGB", "D", "ED", "RGB+D", "RGB+ED"):
+            raise ValueError(f"render_mode must be one of RGB, D, ED, RGB+D, RGB+ED, got {render_mode!r}")
+        if viewmat.dim() == 2 and (bg_color is None or bg_color.dim() == 1):
+            # the same call without the round trip through the gsplat-shaped signature ([None] in, squeeze(0) / [0] out)
+            out, alpha, aux = _render_one(self.xyz, self.rotation, self.scaling, self.opacity.view(-1), self.features, viewmat, K,
+                                          W, H, sh_degree, render_mode, bg_color, 0.01, 1e10, 0.3, 0.0, False, "auto", True,
+                                          grad_into)
+            result = {"alpha": alpha, "means2d": aux["splats"][:, 0:2], "radii": aux["radii"],
+                      "visibility_filter": aux["visibility"]}  # = radii > 0, from the projection kernel
+        else:
+            renders, alphas, meta = rasterization(
+                means=self.xyz, quats=self.rotation, scales=self.scaling, opacities=self.opacity.view(-1),
+                colors=self.features, viewmats=viewmat[None], Ks=K[None], width=W, height=H,
+                sh_degree=sh_degree, render_mode=render_mode,
+                backgrounds=None if bg_color is None else bg_color[None], raw_params=True, grad_into=grad_into)
+            out, alpha = renders.squeeze(0), alphas.squeeze(0)  # views both ways (select's backward = zeros + full-image copy)
+            result = {"alpha": alpha, "means2d": meta["means2d"][0], "radii": meta["radii"][0]}
+            result["visibility_filter"] = meta["visibility_filter"][0]  # = radii > 0, from the projection kernel
         if render_mode == "RGB":
             result["render"] = out
         elif render_mode == "D":

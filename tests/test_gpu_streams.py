@@ -124,6 +124,12 @@ def test_store_lazy_zero_grad_equals_eager(pkg, oracle, deg):
     assert _close(step(two, lazy=True), ref)
     st._flat_grad.fill_(3.0)
     assert _close(step(one, lazy=True, summed=True), ref)
+    # under autocast the Function's arguments pass through custom_fwd's cast, which rebuilds containers: the lazy-zero
+    # state must still be the store's own object (a copied flag would make EVERY view overwrite instead of accumulate)
+    st._flat_grad.fill_(11.0)
+    with torch.autocast("cuda", dtype=torch.float16):
+        got = step(one, lazy=True)
+    assert _close(got, ref)
     st._flat_grad.fill_(5.0)
     st.zero_grad(lazy=True)
     assert st.flat_grad.abs().max().item() == 0.0  # no backward ran: the property performs the postponed memset
