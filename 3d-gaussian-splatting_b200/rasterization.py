@@ -44,6 +44,28 @@ class _stage:
         return False
 
 
+class _stage_on:
+    """``_stage(name)`` for a stage launched on ``stream`` by handle: only while a recorder is installed (``active``) is
+    that stream made current around the block, so the recorder's events land on the stream the kernels run on."""
+
+    __slots__ = ("stream", "active", "name", "prev")
+
+    def __init__(self, stream, active: bool, name: str):
+        self.stream, self.active, self.name = stream, active, name
+
+    def __enter__(self):
+        if self.active:
+            self.prev = torch.cuda.current_stream(self.stream.device)
+            torch.cuda.set_stream(self.stream)
+            _lib.stage_timer.begin(self.name)
+
+    def __exit__(self, *exc):
+        if self.active:
+            _lib.stage_timer.end(self.name)
+            torch.cuda.set_stream(self.prev)
+        return False
+
+
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
@@ -79,7 +101,7 @@ def _plain_f32(t: torch.Tensor, dev: torch.device) -> bool:
 
 
 def make_cam(viewmat: torch.Tensor, K: torch.Tensor, width: int, height: int, near_plane: float = 0.01,
-             far_plane: float = 1e10, eps2d: float = 0.3, radius_clip: float = 0.0) -> torch.Tensor:
+             far_plane: float = 1e10, eps2d: float = 0.3, radius_clip: float = 0.0, stream: Optional[int] = None) -> torch.Tensor:
     """Packed DEVICE camera block (include/b200splat.h, b200_cam_pack).  The pose and the intrinsics are
     consumed on the device — like gsplat, which takes ``viewmats``/``Ks`` as CUDA tensors
     (gsplat_backend.py:174-175) — so rendering a view never synchronises on them.  CPU tensors are uploaded."""
@@ -93,13 +115,10 @@ def make_cam(viewmat: torch.Tensor, K: torch.Tensor, width: int, height: int, ne
     if vm.numel() != 16 or Kd.numel() != 9:
         raise ValueError("make_cam: viewmat must be [4,4] and K [3,3]")
     cam = torch.empty(_lib.CAM_DEV_FLOATS, dtype=torch.float32, device=dev)
-    if torch.cuda.current_device() == dev.index:
+    with _on_device(dev):
         check(lib.b200_cam_pack(_ptr(vm), _ptr(Kd), float(near_plane), float(far_plane), float(eps2d),
-                                float(radius_clip), int(width), int(height), _ptr(cam), _stream()), "b200_cam_pack")
-    else:
-        with torch.cuda.device(dev):
-            check(lib.b200_cam_pack(_ptr(vm), _ptr(Kd), float(near_plane), float(far_plane), float(eps2d),
-                                    float(radius_clip), int(width), int(height), _ptr(cam), _stream()), "b200_cam_pack")
+                                float(radius_clip), int(width), int(height), _ptr(cam), _stream() if stream is None else stream),
+              "b200_cam_pack")
     return cam
 
 
@@ -126,7 +145,7 @@ def _side_stream(dev: torch.device) -> torch.cuda.Stream:
     projection and run UNDER the depth sort of the launching stream (forked and joined with events)."""
     s = _SIDE_STREAMS.get(dev)
     if s is None:
-        s = torch.cuda.Stream(device=dev)
+        s = torch.cuda.Stream(device=dev, priority=-1 if FRONT_PRIORITY else 0)
         _SIDE_STREAMS[dev] = s
     return s
 
@@ -171,12 +190,16 @@ def _carve(dev: torch.device, sizes):
     return owner, [base + o for o in offs]
 
 
-# B200_FRONT_PRIORITY=1: the kernels up to the read-back of M (projection, tile_count, tile_prep) and the sorts / binning run
-# on HIGH-PRIORITY companions of the caller's stream.  With the views of a step in flight on alternating streams
-# (streams.ViewStreams) the block scheduler then places their few CTAs as soon as CTAs of the other view's blend retire
-# instead of behind that blend's last CTA, which is what the host waits for before it can size the intersection buffers.
-# Memory stays in the caller's stream pool (only the launches move), ordered by events both ways.
-FRONT_PRIORITY = int(os.environ.get("B200_FRONT_PRIORITY", "0"))
+# FRONT_PRIORITY (default on; B200_FRONT_PRIORITY=0 turns it off): everything of a view up to the forward blend — camera
+# block, projection, tile_count / tile_prep (the read-back of M), depth sort, two-level binning — is LAUNCHED on
+# high-priority companions of the caller's stream.  The block scheduler hands the SM slots that free up to the oldest
+# pending kernel first, so with the views of a step in flight on alternating streams (streams.ViewStreams) these short
+# latency-bound kernels used to wait behind every not-yet-dispatched CTA of the other view's blend and ran in its drain
+# phase only (and the host, which needs M to size the intersection buffers, waited with them).  With priority their few CTAs
+# are placed as blend CTAs retire: a view's front end runs UNDER the previous view's backward blend.  Measured at config A
+# (profiles/overlap_trace.py, r02 notes): 4-view step 4.65 -> 4.35 ms.  Memory stays in the caller's stream pool (only the
+# launches move), ordered by events both ways; on one stream it changes nothing but two event records.
+FRONT_PRIORITY = int(os.environ.get("B200_FRONT_PRIORITY", "1"))
 _FRONT_STREAMS = {}
 
 
@@ -189,6 +212,16 @@ def _front_stream(dev: torch.device, cur: torch.cuda.Stream) -> torch.cuda.Strea
     return s
 
 
+def _enter_front(dev: torch.device) -> torch.cuda.Stream:
+    """The high-priority companion of the current stream, ordered after everything queued on the current stream so far."""
+    cur = torch.cuda.current_stream(dev)
+    front = _front_stream(dev, cur)
+    enter = torch.cuda.Event()
+    enter.record(cur)
+    front.wait_event(enter)
+    return front
+
+
 def _project_and_bin_coarse(means, quats, scales, opacities, colors, sh_coeffs: int, deg: int, cam, width: int, height: int,
                             tile_w: int, tile_h: int, N: int, raw: bool, want_grad_records: bool, coarse_gather: bool,
                             with_isect_ids: bool, dev: torch.device) -> Dict[str, torch.Tensor]:
@@ -198,12 +231,7 @@ def _project_and_bin_coarse(means, quats, scales, opacities, colors, sh_coeffs: 
     b200_tile_prep itself (unified addressing: the pinned scalar is device-visible), so there is no copy to enqueue."""
     n_tiles = tile_w * tile_h
     cur = torch.cuda.current_stream(dev)
-    launch = cur
-    if FRONT_PRIORITY:
-        launch = _front_stream(dev, cur)
-        enter = torch.cuda.Event()
-        enter.record(cur)
-        launch.wait_event(enter)
+    launch = _enter_front(dev) if FRONT_PRIORITY else cur
     st = launch.cuda_stream
     n1 = max(N, 1)
     i32, f32 = torch.int32, torch.float32
@@ -219,7 +247,10 @@ def _project_and_bin_coarse(means, quats, scales, opacities, colors, sh_coeffs: 
     if coarse_gather:
         p_rects = None
     project_fwd = lib.b200_project_sh_fwd_raw if raw else lib.b200_project_sh_fwd  # raw: activations fused in
-    with _stage("project_sh_fwd"):
+    # bench's per-stage events are recorded on the CURRENT stream: while a recorder is installed, each stage makes the stream
+    # it launches on current (no allocation happens inside those blocks, so every buffer stays in the caller's pool)
+    timed = _lib.stage_timer is not None
+    with _stage_on(launch, timed, "project_sh_fwd"):
         check(project_fwd(_ptr(means), _ptr(quats), _ptr(scales), _ptr(opacities), _ptr(colors), sh_coeffs, deg, N, None,
                           _ptr(cam), width, height, _ptr(radii), _ptr(splats), _ptr(tiles_per_gauss), None, p_dkeys_a, p_gids_a,
                           None if GRID_ON_SIDE_STREAM else p_grid, _ptr(visibility), _ptr(grad_records), p_rects, st),
@@ -233,49 +264,36 @@ def _project_and_bin_coarse(means, quats, scales, opacities, colors, sh_coeffs: 
     side.wait_event(fork)
     sst = side.cuda_stream
     m_host = _pinned_scalar(dev)
-    timed = _lib.stage_timer is not None  # bench's per-stage events are recorded on the CURRENT stream
-    if timed:
-        torch.cuda.set_stream(side)
-    try:
-        if GRID_ON_SIDE_STREAM:  # the corner grid is counted here, not inside the projection kernel (b200_tile_count)
-            with _stage("tile_count"):
-                check(lib.b200_tile_count(_ptr(splats), _ptr(radii), N, width, height, p_grid, sst), "b200_tile_count",
-                      kernels=1 if N > 0 else 0)
-        with _stage("tile_prep"):
-            check(lib.b200_tile_prep(p_grid, width, height, _ptr(offsets), m_host.data_ptr(), p_digit, sst), "b200_tile_prep")
-    finally:
-        if timed:
-            torch.cuda.set_stream(cur)
+    if GRID_ON_SIDE_STREAM:  # the corner grid is counted here, not inside the projection kernel (b200_tile_count)
+        with _stage_on(side, timed, "tile_count"):
+            check(lib.b200_tile_count(_ptr(splats), _ptr(radii), N, width, height, p_grid, sst), "b200_tile_count",
+                  kernels=1 if N > 0 else 0)
+    with _stage_on(side, timed, "tile_prep"):
+        check(lib.b200_tile_prep(p_grid, width, height, _ptr(offsets), m_host.data_ptr(), p_digit, sst), "b200_tile_prep")
     m_ready = torch.cuda.Event()
     m_ready.record(side)
     in_b = C.c_int(0)
-    if timed and launch is not cur:
-        torch.cuda.set_stream(launch)
-    try:
-        with _stage("sort_depth"):
-            check(lib.b200_sort_pairs_k32(p_dkeys_a, p_gids_a, p_dkeys_b, p_gids_b, N, 32, p_sort, sort_bytes, C.byref(in_b), st),
-                  "b200_sort_pairs_k32", kernels=6 if N > 0 else 0)
-        p_perm = p_gids_b if in_b.value else p_gids_a
-        launch.wait_event(m_ready)  # join: ranges / digit bases are used from here on
-        m_ready.synchronize()  # the one host wait of the forward pass (sizes the intersection buffers)
-        M = int(m_host.item())
-        cap = max(M, 1)
-        flat_ids = torch.empty(cap, dtype=i32, device=dev)
-        sb = max(int(lib.b200_bin_coarse_scratch_bytes(N, M)), 256)
-        ws2, (p_k0, p_k1, p_k2, p_k3, p_scr) = _carve(dev, (4 * cap, 4 * cap, 4 * cap, 4 * cap, sb))
-        with _stage("bin_coarse"):
-            check(lib.b200_bin_coarse(_ptr(splats), _ptr(radii), p_rects, p_perm, N, width, height, _ptr(offsets), M,
-                                      p_k0, p_k1, p_k2, p_k3, _ptr(flat_ids), p_scr, sb, st), "b200_bin_coarse",
-                  kernels=(3 + (2 if n_tiles > 16 * 256 else 1)) if (N > 0 and M > 0) else 0)
-        ids = None
-        if with_isect_ids:
-            ids = torch.empty(cap, dtype=torch.int64, device=dev)
-            check(lib.b200_isect_ids_from_offsets(_ptr(flat_ids), _ptr(offsets), n_tiles, _ptr(splats), M, _ptr(ids), st),
-                  "b200_isect_ids_from_offsets", kernels=1 if M > 0 else 0)
-            ids = ids[:M]
-    finally:
-        if timed and launch is not cur:
-            torch.cuda.set_stream(cur)
+    with _stage_on(launch, timed, "sort_depth"):
+        check(lib.b200_sort_pairs_k32(p_dkeys_a, p_gids_a, p_dkeys_b, p_gids_b, N, 32, p_sort, sort_bytes, C.byref(in_b), st),
+              "b200_sort_pairs_k32", kernels=6 if N > 0 else 0)
+    p_perm = p_gids_b if in_b.value else p_gids_a
+    launch.wait_event(m_ready)  # join: ranges / digit bases are used from here on
+    m_ready.synchronize()  # the one host wait of the forward pass (sizes the intersection buffers)
+    M = int(m_host.item())
+    cap = max(M, 1)
+    flat_ids = torch.empty(cap, dtype=i32, device=dev)
+    sb = max(int(lib.b200_bin_coarse_scratch_bytes(N, M)), 256)
+    ws2, (p_k0, p_k1, p_k2, p_k3, p_scr) = _carve(dev, (4 * cap, 4 * cap, 4 * cap, 4 * cap, sb))
+    with _stage_on(launch, timed, "bin_coarse"):
+        check(lib.b200_bin_coarse(_ptr(splats), _ptr(radii), p_rects, p_perm, N, width, height, _ptr(offsets), M,
+                                  p_k0, p_k1, p_k2, p_k3, _ptr(flat_ids), p_scr, sb, st), "b200_bin_coarse",
+              kernels=(3 + (2 if n_tiles > 16 * 256 else 1)) if (N > 0 and M > 0) else 0)
+    ids = None
+    if with_isect_ids:
+        ids = torch.empty(cap, dtype=torch.int64, device=dev)
+        check(lib.b200_isect_ids_from_offsets(_ptr(flat_ids), _ptr(offsets), n_tiles, _ptr(splats), M, _ptr(ids), st),
+              "b200_isect_ids_from_offsets", kernels=1 if M > 0 else 0)
+        ids = ids[:M]
     if launch is not cur:
         leave = torch.cuda.Event()
         leave.record(launch)
@@ -629,7 +647,11 @@ def _render_one(means, quats, scales, opacities, colors, viewmat, K, width, heig
         if bgt.numel() < 3:
             raise ValueError("backgrounds must hold 3 colour channels")
         bg = (bgt, 3)
-    cam = make_cam(viewmat, K, int(width), int(height), near_plane, far_plane, eps2d, radius_clip)
+    # (FRONT_PRIORITY: the camera block is packed on the high-priority companion stream too — a one-CTA kernel on the
+    # caller's stream would wait behind every CTA of the other view's blend, and the projection behind it)
+    front = _enter_front(means.device).cuda_stream if (FRONT_PRIORITY and method in ("auto", "coarse", "coarse-gather")
+                                                       and _coarse_supported(int(width), int(height))) else None
+    cam = make_cam(viewmat, K, int(width), int(height), near_plane, far_plane, eps2d, radius_clip, stream=front)
     aux = _Aux()
     render, alpha = RasterizeSplats.apply(means, quats, scales, opacities, colors, cam, int(width), int(height), sh_degree,
                                           chset, bg, with_isect_ids, method, raw, grad_into, aux)
