@@ -352,11 +352,23 @@ def run_b200(args):
             ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
             ev[0].record()
         vstreams.begin()
-        for v in range(V):
-            with vstreams.view(v):
-                vp = {"world_view_transform": poses_dev[my_view(step, v)], "image_width": W, "image_height": H}
-                res = backend.render_with_depth(leaves, vp, bg_color=bg, render_mode="RGB", device="cuda", sh_degree=deg)
-                res["render"].backward(v_render)
+        if args.batched_backward:  # the reference's order (trainer.py:458-506): every view rendered, then the backward passes
+            outs = []
+            for v in range(V):
+                with vstreams.view(v):
+                    vp = {"world_view_transform": poses_dev[my_view(step, v)], "image_width": W, "image_height": H}
+                    outs.append(backend.render_with_depth(leaves, vp, bg_color=bg, render_mode="RGB", device="cuda",
+                                                          sh_degree=deg)["render"])
+            for v in reversed(range(V)):
+                with vstreams.view(v):
+                    outs[v].backward(v_render)
+            del outs
+        else:
+            for v in range(V):
+                with vstreams.view(v):
+                    vp = {"world_view_transform": poses_dev[my_view(step, v)], "image_width": W, "image_height": H}
+                    res = backend.render_with_depth(leaves, vp, bg_color=bg, render_mode="RGB", device="cuda", sh_degree=deg)
+                    res["render"].backward(v_render)
         vstreams.join()
         if probe["on"]:
             ev[1].record()
@@ -773,6 +785,7 @@ def main():
                     help="N>1, train leg: NCCL all-reduce + Adam on every rank instead of the fused multimem optimiser kernel")
     ap.add_argument("--no-balance", action="store_true",
                     help="N>1: deal the cameras of a step to the ranks in plain order instead of balancing them by M")
+    ap.add_argument("--batched-backward", action="store_true", help="value leg: render every view of a step first, then run the backward passes (the reference trainer's order) instead of render+backward per view")
     ap.add_argument("--no-reference-trainer", action="store_true",
                     help="skip the leg that times the reference's unmodified _training_step on B200Backend")
     ap.add_argument("--total-views", type=int, default=0,
