@@ -692,6 +692,13 @@ def run_b200(args):
                                        "flight on alternating streams: a bracket also holds whatever the other view ran in between. "
                                        "'stages_one_stream_ms' is the same step on ONE stream (separate short pass, not the headline).")
             roofline["stages_one_stream_ms"] = {k: round(t1[k] / max(c1[k], 1), 4) for k in t1}
+            # the dominant kernel timed ALONE on its stream (one-stream pass): in the timed region it shares the SMs with the
+            # next view's front end (FRONT_PRIORITY), so its launches there last longer than the kernel by itself
+            alone_ms = roofline["stages_one_stream_ms"].get(dom)
+            if alone_ms:
+                ach1 = alg.get(dom, 0) / (alone_ms * 1e-3) / 1e9
+                roofline["achieved_alone"] = round(ach1, 1)
+                roofline["frac_alone"] = round(ach1 / hbm, 4)
 
     cpu_baseline = None
     try:
